@@ -1,0 +1,618 @@
+"""Module model: what one Terraform module directory declares.
+
+A Terraform *module* is all ``*.tf`` files of one directory read as a single
+configuration.  The reference has six of them: ``eks/``, ``gke/``, ``aks/`` and
+one ``examples/cnpack`` below each.  This loader restates the
+structural rules of Terraform's configuration loader (top-level block schema,
+label counts, name syntax, duplicate declarations, meta-arguments) -- the part
+of ``terraform validate`` that needs no provider plugin.  Provider schemas are
+NOT available offline, so arguments *inside* resource/data/provider bodies are
+never judged; DESIGN.md lists what that leaves unchecked.
+"""
+from __future__ import annotations
+
+import os
+from dataclasses import dataclass, field
+from typing import Optional
+
+from ..hcl import ast as A
+from ..hcl.diagnostics import Diagnostic, ERROR, WARNING
+from ..hcl.parser import parse
+from ..hcl.scanner import is_valid_identifier
+from ..hcl.tokens import Token
+from . import typeexpr
+from .versions import Constraints, try_parse_constraints
+
+_BAD_NAME = ("A name must start with a letter or underscore and may contain only letters, digits, "
+             "underscores, and dashes.")
+
+# top-level block types -> number of labels
+TOP_LEVEL_BLOCKS = {
+    "terraform": 0, "provider": 1, "variable": 1, "locals": 0, "output": 1, "module": 1,
+    "resource": 2, "data": 2, "moved": 0, "import": 0, "check": 1, "removed": 0, "ephemeral": 2,
+}
+RESERVED_VARIABLE_NAMES = {"source", "version", "providers", "count", "for_each", "lifecycle",
+                           "depends_on", "locals"}
+VARIABLE_ARGS = {"description", "default", "type", "sensitive", "nullable", "ephemeral"}
+OUTPUT_ARGS = {"description", "value", "sensitive", "depends_on", "ephemeral"}
+LIFECYCLE_ARGS = {"create_before_destroy", "prevent_destroy", "ignore_changes", "replace_triggered_by"}
+RESOURCE_META_ARGS = {"count", "for_each", "provider", "depends_on"}
+MODULE_META_ARGS = {"source", "version", "count", "for_each", "depends_on", "providers"}
+
+
+@dataclass
+class SourceFile:
+    path: str                 # display path
+    src: str
+    body: A.Body
+    tokens: list[Token]
+
+
+@dataclass
+class Decl:
+    """Anything declared by a block or attribute, with where it was declared."""
+    name: str
+    file: str
+    line: int
+    block: Optional[A.Block] = None
+    attr: Optional[A.Attribute] = None
+
+
+@dataclass
+class Variable(Decl):
+    type: Optional[typeexpr.Type] = None
+    has_default: bool = False
+    default: object = None
+    description: Optional[str] = None
+    sensitive: bool = False
+    nullable: Optional[bool] = None
+
+    @property
+    def required(self) -> bool:
+        return not self.has_default
+
+
+@dataclass
+class Output(Decl):
+    description: Optional[str] = None
+    sensitive: bool = False
+
+
+@dataclass
+class Resource(Decl):
+    mode: str = "managed"     # managed | data
+    type: str = ""
+    has_count: bool = False
+    has_for_each: bool = False
+    provider_ref: Optional[str] = None      # provider = google-beta / aws.west
+
+    @property
+    def addr(self) -> str:
+        return ("data." if self.mode == "data" else "") + f"{self.type}.{self.name}"
+
+    @property
+    def implied_provider(self) -> str:
+        if self.provider_ref:
+            return self.provider_ref.split(".")[0]
+        return self.type.split("_", 1)[0]
+
+
+@dataclass
+class ModuleCall(Decl):
+    source: Optional[str] = None
+    version: Optional[str] = None
+    has_count: bool = False
+    has_for_each: bool = False
+
+    @property
+    def is_local(self) -> bool:
+        return bool(self.source) and (self.source.startswith("./") or self.source.startswith("../")
+                                      or self.source in (".", ".."))
+
+    @property
+    def is_registry(self) -> bool:
+        s = self.source or ""
+        if self.is_local or "::" in s or s.startswith(("git@", "http://", "https://", "github.com/",
+                                                       "bitbucket.org/", "/")):
+            return False
+        parts = s.split("//", 1)[0].split("/")
+        return len(parts) in (3, 4)
+
+
+@dataclass
+class ProviderConfig(Decl):
+    alias: Optional[str] = None
+
+
+@dataclass
+class RequiredProvider(Decl):
+    source: Optional[str] = None
+    constraint_text: Optional[str] = None
+    constraints: Optional[Constraints] = None
+
+    @property
+    def fqn(self) -> str:
+        """registry.terraform.io/<namespace>/<type>"""
+        src = self.source or f"hashicorp/{self.name}"
+        parts = src.split("/")
+        if len(parts) == 1:
+            parts = ["hashicorp"] + parts
+        if len(parts) == 2:
+            parts = ["registry.terraform.io"] + parts
+        return "/".join(parts).lower()     # provider addresses compare case-insensitively
+
+
+@dataclass
+class Module:
+    dir: str
+    files: list[SourceFile] = field(default_factory=list)
+    variables: dict[str, Variable] = field(default_factory=dict)
+    locals: dict[str, Decl] = field(default_factory=dict)
+    outputs: dict[str, Output] = field(default_factory=dict)
+    resources: dict[str, Resource] = field(default_factory=dict)     # keyed by addr
+    module_calls: dict[str, ModuleCall] = field(default_factory=dict)
+    providers: list[ProviderConfig] = field(default_factory=list)
+    required_providers: dict[str, RequiredProvider] = field(default_factory=dict)
+    required_versions: list[tuple[str, Decl]] = field(default_factory=list)
+    diags: list[Diagnostic] = field(default_factory=list)
+
+    def used_provider_names(self) -> dict[str, list[Resource]]:
+        out: dict[str, list[Resource]] = {}
+        for r in self.resources.values():
+            out.setdefault(r.implied_provider, []).append(r)
+        return out
+
+
+# ---------------------------------------------------------------------------
+class _Loader:
+    def __init__(self, directory: str, display_root: Optional[str] = None):
+        self.m = Module(directory)
+        self.root = display_root
+
+    def diag(self, sev: str, summary: str, detail: str, file: str, node, rule: str) -> None:
+        line = node.pos.line if isinstance(node, A.Node) else int(node)
+        col = node.pos.col if isinstance(node, A.Node) else 0
+        self.m.diags.append(Diagnostic(sev, summary, detail, file, line, col, rule))
+
+    def display(self, path: str) -> str:
+        if self.root:
+            return os.path.relpath(path, self.root)
+        return path
+
+    def load(self) -> Module:
+        try:
+            names = sorted(os.listdir(self.m.dir))
+        except OSError as e:
+            self.m.diags.append(Diagnostic(ERROR, "Failed to read module directory",
+                                           f"Module directory {self.m.dir} does not exist or cannot be read: {e}",
+                                           self.m.dir, rule="module-dir"))
+            return self.m
+        tf = [n for n in names if n.endswith(".tf") and not n.startswith((".", "~", "#"))]
+        for name in tf:
+            path = os.path.join(self.m.dir, name)
+            with open(path, "r", encoding="utf-8", newline="") as fh:
+                src = fh.read()
+            disp = self.display(path)
+            body, diags, tokens = parse(src, disp)
+            self.m.diags.extend(diags)
+            self.m.files.append(SourceFile(disp, src, body, tokens))
+        for f in self.m.files:
+            self.top_level(f)
+        return self.m
+
+    # -- top level -----------------------------------------------------------
+    def top_level(self, f: SourceFile) -> None:
+        for item in f.body.items:
+            if isinstance(item, A.Attribute):
+                self.diag(ERROR, "Unsupported argument",
+                          f"An argument named \"{item.name}\" is not expected here.", f.path, item, "structure")
+                continue
+            want = TOP_LEVEL_BLOCKS.get(item.type)
+            if want is None:
+                self.diag(ERROR, "Unsupported block type",
+                          f"Blocks of type \"{item.type}\" are not expected here.", f.path, item, "structure")
+                continue
+            if not self.check_labels(f, item, want):
+                continue
+            getattr(self, "block_" + item.type, self.block_other)(f, item)
+
+    def check_labels(self, f: SourceFile, b: A.Block, want: int) -> bool:
+        want_names = "type, name" if want == 2 else "name"
+        if len(b.labels) < want:
+            missing = "type" if want == 2 and not b.labels else "name"
+            self.diag(ERROR, f"Missing {missing} for {b.type}",
+                      f"All {b.type} blocks must have {want} labels ({want_names}).", f.path, b, "structure")
+            return False
+        if len(b.labels) > want:
+            detail = (f"Only {want} labels ({want_names}) are expected for {b.type} blocks." if want
+                      else f"No labels are expected for {b.type} blocks.")
+            self.diag(ERROR, f"Extraneous label for {b.type}", detail, f.path, b, "structure")
+            return False
+        return True
+
+    def check_name(self, f: SourceFile, b: A.Block, value: str, what: str) -> bool:
+        if not is_valid_identifier(value):
+            self.diag(ERROR, f"Invalid {what}", _BAD_NAME, f.path, b, "structure")
+            return False
+        return True
+
+    def check_args(self, f: SourceFile, b: A.Block, allowed: set[str], blocks: dict[str, int]) -> None:
+        for item in b.body.items:
+            if isinstance(item, A.Attribute):
+                if item.name not in allowed:
+                    self.diag(ERROR, "Unsupported argument",
+                              f"An argument named \"{item.name}\" is not expected here.", f.path, item, "structure")
+            elif item.type not in blocks:
+                self.diag(ERROR, "Unsupported block type",
+                          f"Blocks of type \"{item.type}\" are not expected here.", f.path, item, "structure")
+            elif len(item.labels) != blocks[item.type]:
+                self.diag(ERROR, f"Wrong number of labels for {item.type}",
+                          f"{item.type} blocks take {blocks[item.type]} label(s).", f.path, item, "structure")
+        seen: dict[str, A.Attribute] = {}
+        for item in b.body.items:
+            if isinstance(item, A.Attribute):
+                if item.name in seen:
+                    self.diag(ERROR, "Attribute redefined",
+                              f"The argument \"{item.name}\" was already set at {f.path}:{seen[item.name].pos.line}. "
+                              "Each argument may be set only once.", f.path, item, "structure")
+                seen.setdefault(item.name, item)
+
+    def duplicate(self, f: SourceFile, b: A.Node, table: dict, key: str, summary: str, detail: str) -> bool:
+        if key in table:
+            prev = table[key]
+            self.diag(ERROR, summary, detail.format(prev=f"{prev.file}:{prev.line}"), f.path, b, "duplicate")
+            return True
+        return False
+
+    def literal(self, f: SourceFile, attr: A.Attribute, kind: type, what: str):
+        v = typeexpr.literal_value(attr.expr)
+        if v is typeexpr.UNKNOWN:
+            self.no_variables(f, attr.expr)
+            return None
+        if kind is bool and isinstance(v, str) and v in ("true", "false"):
+            v = v == "true"
+        if not isinstance(v, kind) or (kind is not bool and isinstance(v, bool)):
+            self.diag(ERROR, f"Invalid {what}", f"A {kind.__name__ if kind is not str else 'string'} "
+                      f"value is required for \"{attr.name}\".", f.path, attr.expr, "structure")
+            return None
+        return v
+
+    def no_variables(self, f: SourceFile, expr: A.Expr) -> None:
+        for node in expr.walk():
+            if isinstance(node, A.ScopeTraversal):
+                self.diag(ERROR, "Variables not allowed", "Variables may not be used here.",
+                          f.path, node, "structure")
+                return
+            if isinstance(node, A.FunctionCall):
+                self.diag(ERROR, "Function calls not allowed", "Functions may not be called here.",
+                          f.path, node, "structure")
+                return
+
+    # -- block handlers ----------------------------------------------------
+    def block_other(self, f: SourceFile, b: A.Block) -> None:
+        pass
+
+    def block_variable(self, f: SourceFile, b: A.Block) -> None:
+        name = b.labels[0].value
+        if not self.check_name(f, b, name, "variable name"):
+            return
+        if name in RESERVED_VARIABLE_NAMES:
+            self.diag(ERROR, "Invalid variable name",
+                      f"The variable name \"{name}\" is reserved due to its special meaning inside module blocks.",
+                      f.path, b, "structure")
+        self.check_args(f, b, VARIABLE_ARGS, {"validation": 0})
+        if self.duplicate(f, b, self.m.variables, name, "Duplicate variable declaration",
+                          f"A variable named \"{name}\" was already declared at {{prev}}. "
+                          "Variable names must be unique within a module."):
+            return
+        v = Variable(name, f.path, b.pos.line, block=b)
+        attrs = b.body.attributes
+        if "type" in attrs:
+            try:
+                v.type = typeexpr.parse_type(attrs["type"].expr)
+            except typeexpr.TypeError_ as e:
+                self.diag(ERROR, "Invalid type specification", str(e), f.path, e.node, "type")
+        if "description" in attrs:
+            v.description = self.literal(f, attrs["description"], str, "description")
+        if "sensitive" in attrs:
+            v.sensitive = bool(self.literal(f, attrs["sensitive"], bool, "sensitive flag"))
+        if "nullable" in attrs:
+            v.nullable = self.literal(f, attrs["nullable"], bool, "nullable flag")
+        if "default" in attrs:
+            v.has_default = True
+            self.no_variables(f, attrs["default"].expr)
+            v.default = typeexpr.literal_value(attrs["default"].expr)
+            if v.type is not None:
+                err = typeexpr.conformance_error(v.default, v.type)
+                if err:
+                    self.diag(ERROR, "Invalid default value for variable",
+                              f"This default value is not compatible with the variable's type constraint: {err}.",
+                              f.path, attrs["default"].expr, "type")
+            if v.default is None and v.nullable is False:
+                self.diag(ERROR, "Invalid default value for variable",
+                          "A null default value is not valid when nullable=false.",
+                          f.path, attrs["default"].expr, "type")
+        self.m.variables[name] = v
+
+    def block_locals(self, f: SourceFile, b: A.Block) -> None:
+        for item in b.body.items:
+            if isinstance(item, A.Block):
+                self.diag(ERROR, "Unsupported block type",
+                          f"Blocks of type \"{item.type}\" are not expected here.", f.path, item, "structure")
+                continue
+            if not is_valid_identifier(item.name):
+                self.diag(ERROR, "Invalid local value name", _BAD_NAME, f.path, item, "structure")
+                continue
+            if self.duplicate(f, item, self.m.locals, item.name, "Duplicate local value definition",
+                              f"A local value named \"{item.name}\" was already defined at {{prev}}. "
+                              "Local value names must be unique within a module."):
+                continue
+            self.m.locals[item.name] = Decl(item.name, f.path, item.pos.line, attr=item)
+
+    def block_output(self, f: SourceFile, b: A.Block) -> None:
+        name = b.labels[0].value
+        if not self.check_name(f, b, name, "output name"):
+            return
+        self.check_args(f, b, OUTPUT_ARGS, {"precondition": 0})
+        attrs = b.body.attributes
+        if "value" not in attrs:
+            self.diag(ERROR, "Missing required argument",
+                      "The argument \"value\" is required, but no definition was found.", f.path, b, "structure")
+        if self.duplicate(f, b, self.m.outputs, name, "Duplicate output definition",
+                          f"An output named \"{name}\" was already defined at {{prev}}. "
+                          "Output names must be unique within a module."):
+            return
+        o = Output(name, f.path, b.pos.line, block=b)
+        if "description" in attrs:
+            o.description = self.literal(f, attrs["description"], str, "description")
+        if "sensitive" in attrs:
+            o.sensitive = bool(self.literal(f, attrs["sensitive"], bool, "sensitive flag"))
+        self.m.outputs[name] = o
+
+    def _count_for_each(self, f: SourceFile, b: A.Block) -> tuple[bool, bool]:
+        attrs = b.body.attributes
+        has_count, has_each = "count" in attrs, "for_each" in attrs
+        if has_count and has_each:
+            self.diag(ERROR, "Invalid combination of \"count\" and \"for_each\"",
+                      "The \"count\" and \"for_each\" meta-arguments are mutually-exclusive, only one should "
+                      "be used to be explicit about how many instances are to be created.",
+                      f.path, attrs["for_each"], "structure")
+        return has_count, has_each
+
+    def block_module(self, f: SourceFile, b: A.Block) -> None:
+        name = b.labels[0].value
+        if not self.check_name(f, b, name, "module instance name"):
+            return
+        if self.duplicate(f, b, self.m.module_calls, name, "Duplicate module call",
+                          f"A module call named \"{name}\" was already defined at {{prev}}. "
+                          "Module calls must have unique names within a module."):
+            return
+        mc = ModuleCall(name, f.path, b.pos.line, block=b)
+        attrs = b.body.attributes
+        mc.has_count, mc.has_for_each = self._count_for_each(f, b)
+        if "source" not in attrs:
+            self.diag(ERROR, "Missing required argument",
+                      "The argument \"source\" is required, but no definition was found.", f.path, b, "structure")
+        else:
+            mc.source = self.literal(f, attrs["source"], str, "module source")
+        if "version" in attrs:
+            mc.version = self.literal(f, attrs["version"], str, "version constraint")
+            if mc.version is not None:
+                cons, err = try_parse_constraints(mc.version)
+                if cons is None:
+                    self.diag(ERROR, "Invalid version constraint",
+                              f"This string does not use correct version constraint syntax: {err}.",
+                              f.path, attrs["version"].expr, "version")
+                if mc.source is not None and not mc.is_registry:
+                    self.diag(ERROR, "Invalid registry module source address",
+                              f"Cannot apply a version constraint to module \"{name}\" because its source "
+                              f"\"{mc.source}\" is not a module registry address.",
+                              f.path, attrs["version"], "version")
+        for blk in b.body.blocks:
+            if blk.type in ("lifecycle", "locals", "provider", "dynamic"):
+                self.diag(ERROR, "Reserved block type name in module block" if blk.type != "dynamic"
+                          else "Unsupported block type",
+                          f"The block type name \"{blk.type}\" is reserved for use by Terraform in a future version."
+                          if blk.type != "dynamic" else
+                          f"Blocks of type \"{blk.type}\" are not expected here.", f.path, blk, "structure")
+            else:
+                self.diag(ERROR, "Unsupported block type",
+                          f"Blocks of type \"{blk.type}\" are not expected here.", f.path, blk, "structure")
+        self.m.module_calls[name] = mc
+
+    def _resource(self, f: SourceFile, b: A.Block, mode: str) -> None:
+        typ, name = b.labels[0].value, b.labels[1].value
+        word = "data source" if mode == "data" else "resource"
+        if not self.check_name(f, b, typ, f"{word} type name" if mode == "managed" else "data source name"):
+            return
+        if not self.check_name(f, b, name, f"{word} name"):
+            return
+        r = Resource(name, f.path, b.pos.line, block=b, mode=mode, type=typ)
+        kind = "data" if mode == "data" else "resource"
+        if self.duplicate(f, b, self.m.resources, r.addr,
+                          f"Duplicate {kind} \"{typ}\" configuration",
+                          f"A {typ} {word} named \"{name}\" was already declared at {{prev}}. "
+                          f"Resource names must be unique per type in each module."):
+            return
+        attrs = b.body.attributes
+        r.has_count, r.has_for_each = self._count_for_each(f, b)
+        if "provider" in attrs:
+            e = attrs["provider"].expr
+            if isinstance(e, A.ScopeTraversal) and len(e.steps) <= 1 and all(s.kind == "attr" for s in e.steps):
+                r.provider_ref = e.dotted()
+            elif isinstance(e, A.Template) and e.literal_value() is not None:
+                r.provider_ref = e.literal_value()
+                self.diag(WARNING, "Quoted references are deprecated",
+                          "In this context, references are expected literally rather than in quotes. "
+                          "Terraform 0.11 and earlier required quotes, but quoted references are now "
+                          "deprecated and will be removed in a future version of Terraform. Remove the "
+                          "quotes surrounding this reference to silence this warning.", f.path, e, "deprecated")
+            else:
+                self.diag(ERROR, "Invalid provider configuration reference",
+                          "The provider argument requires a provider type name, optionally followed by a "
+                          "period and then a configuration alias.", f.path, e, "structure")
+        seen_lifecycle = False
+        for blk in b.body.blocks:
+            if blk.type == "lifecycle":
+                if seen_lifecycle:
+                    self.diag(ERROR, "Duplicate lifecycle block",
+                              "This resource already has a lifecycle block.", f.path, blk, "structure")
+                seen_lifecycle = True
+                self.check_args(f, blk, LIFECYCLE_ARGS if mode == "managed" else set(),
+                                {"precondition": 0, "postcondition": 0})
+            elif blk.type in ("provisioner", "connection") and mode == "data":
+                self.diag(ERROR, "Unsupported block type" if blk.type == "connection"
+                          else "Data resources do not have provisioners",
+                          "Data resources do not have provisioners." if blk.type == "provisioner" else
+                          f"Blocks of type \"{blk.type}\" are not expected here.", f.path, blk, "structure")
+            elif blk.type == "provisioner":
+                if len(blk.labels) != 1:
+                    self.diag(ERROR, "Missing type for provisioner" if not blk.labels
+                              else "Extraneous label for provisioner",
+                              "All provisioner blocks must have 1 labels (type).", f.path, blk, "structure")
+            elif blk.type == "dynamic":
+                self.check_dynamic(f, blk)
+        self._walk_dynamic(f, b.body)
+        self.m.resources[r.addr] = r
+
+    def _walk_dynamic(self, f: SourceFile, body: A.Body) -> None:
+        for blk in body.blocks:
+            if blk.type == "dynamic":
+                self.check_dynamic(f, blk)
+            self._walk_dynamic(f, blk.body)
+
+    def check_dynamic(self, f: SourceFile, blk: A.Block) -> None:
+        if getattr(blk, "_dyn_checked", False):
+            return
+        blk._dyn_checked = True
+        if len(blk.labels) != 1:
+            self.diag(ERROR, "Invalid dynamic block", "A dynamic block must have exactly one label: "
+                      "the type of block to generate.", f.path, blk, "structure")
+        attrs = blk.body.attributes
+        if "for_each" not in attrs:
+            self.diag(ERROR, "Missing required argument",
+                      "The argument \"for_each\" is required, but no definition was found.", f.path, blk, "structure")
+        for a in attrs:
+            if a not in ("for_each", "iterator", "labels"):
+                self.diag(ERROR, "Unsupported argument",
+                          f"An argument named \"{a}\" is not expected here.", f.path, attrs[a], "structure")
+        content = blk.body.blocks_of("content")
+        if len(content) != 1:
+            self.diag(ERROR, "Insufficient content blocks" if not content else "Too many content blocks",
+                      "At least 1 \"content\" blocks are required." if not content else
+                      "No more than 1 \"content\" blocks are allowed", f.path, blk, "structure")
+        for other in blk.body.blocks:
+            if other.type != "content":
+                self.diag(ERROR, "Unsupported block type",
+                          f"Blocks of type \"{other.type}\" are not expected here.", f.path, other, "structure")
+
+    def block_resource(self, f: SourceFile, b: A.Block) -> None:
+        self._resource(f, b, "managed")
+
+    def block_data(self, f: SourceFile, b: A.Block) -> None:
+        self._resource(f, b, "data")
+
+    def block_provider(self, f: SourceFile, b: A.Block) -> None:
+        name = b.labels[0].value
+        if not self.check_name(f, b, name, "provider configuration name"):
+            return
+        p = ProviderConfig(name, f.path, b.pos.line, block=b)
+        attrs = b.body.attributes
+        if "alias" in attrs:
+            p.alias = self.literal(f, attrs["alias"], str, "provider configuration alias")
+            if p.alias is not None and not is_valid_identifier(p.alias):
+                self.diag(ERROR, "Invalid provider configuration alias",
+                          f"An alias must be a valid name. {_BAD_NAME}", f.path, attrs["alias"].expr, "structure")
+        if "version" in attrs:
+            self.diag(WARNING, "Version constraints inside provider configuration blocks are deprecated",
+                      "Terraform 0.13 and earlier allowed provider version constraints inside the provider "
+                      "configuration block, but that is now deprecated and will be removed in a future version "
+                      "of Terraform. To silence this warning, move the provider version constraint into the "
+                      "required_providers block.", f.path, attrs["version"], "deprecated")
+        for prev in self.m.providers:
+            if prev.name == name and prev.alias == p.alias:
+                self.diag(ERROR, "Duplicate provider configuration",
+                          f"A {'default (non-aliased)' if p.alias is None else 'aliased'} provider configuration "
+                          f"for \"{name}\" was already given at {prev.file}:{prev.line}. If multiple configurations "
+                          "are required, set the \"alias\" argument for alternative configurations.",
+                          f.path, b, "duplicate")
+                return
+        self.m.providers.append(p)
+
+    def block_terraform(self, f: SourceFile, b: A.Block) -> None:
+        self.check_args(f, b, {"required_version", "experiments", "language"},
+                        {"required_providers": 0, "backend": 1, "cloud": 0, "provider_meta": 1,
+                         "encryption": 0})
+        attrs = b.body.attributes
+        if "required_version" in attrs:
+            text = self.literal(f, attrs["required_version"], str, "version constraint")
+            if text is not None:
+                cons, err = try_parse_constraints(text)
+                if cons is None:
+                    self.diag(ERROR, "Invalid version constraint",
+                              f"This string does not use correct version constraint syntax: {err}.",
+                              f.path, attrs["required_version"].expr, "version")
+                else:
+                    self.m.required_versions.append(
+                        (text, Decl("required_version", f.path, attrs["required_version"].pos.line,
+                                    attr=attrs["required_version"])))
+        rp_blocks = b.body.blocks_of("required_providers")
+        for rp in rp_blocks:
+            self.required_providers(f, rp)
+
+    def required_providers(self, f: SourceFile, rp: A.Block) -> None:
+        for blk in rp.body.blocks:
+            self.diag(ERROR, "Unsupported block type",
+                      f"Blocks of type \"{blk.type}\" are not expected here.", f.path, blk, "structure")
+        for item in rp.body.items:
+            if not isinstance(item, A.Attribute):
+                continue
+            name = item.name
+            if not is_valid_identifier(name):
+                self.diag(ERROR, "Invalid provider local name", _BAD_NAME, f.path, item, "structure")
+                continue
+            if name in self.m.required_providers:
+                prev = self.m.required_providers[name]
+                self.diag(ERROR, "Duplicate required providers configuration",
+                          f"A module may have only one required providers configuration. The required providers "
+                          f"were previously configured at {prev.file}:{prev.line}.", f.path, item, "duplicate")
+                continue
+            req = RequiredProvider(name, f.path, item.pos.line, attr=item)
+            val = typeexpr.literal_value(item.expr)
+            if isinstance(val, str):
+                req.constraint_text = val              # legacy: aws = "~> 4.0"
+            elif isinstance(val, dict):
+                for k in val:
+                    if k not in ("source", "version", "configuration_aliases"):
+                        self.diag(ERROR, "Invalid required_providers object",
+                                  "required_providers objects can only contain \"version\", \"source\" and "
+                                  "\"configuration_aliases\" attributes. To configure a provider, use a "
+                                  "\"provider\" block.", f.path, item.expr, "structure")
+                if isinstance(val.get("source"), str):
+                    req.source = val["source"]
+                    parts = req.source.split("/")
+                    if not 1 <= len(parts) <= 3 or any(not p for p in parts):
+                        self.diag(ERROR, "Invalid provider source string",
+                                  "The \"source\" attribute must be in the format \"[hostname/][namespace/]name\"",
+                                  f.path, item.expr, "structure")
+                elif "source" in val and val["source"] is not typeexpr.UNKNOWN:
+                    self.diag(ERROR, "Invalid source", "Source must be specified as a string.",
+                              f.path, item.expr, "structure")
+                if isinstance(val.get("version"), str):
+                    req.constraint_text = val["version"]
+            else:
+                self.diag(ERROR, "Invalid required_providers object",
+                          "required_providers entries must be strings or objects.", f.path, item.expr, "structure")
+                continue
+            if req.constraint_text is not None:
+                req.constraints, err = try_parse_constraints(req.constraint_text)
+                if req.constraints is None:
+                    self.diag(ERROR, "Invalid version constraint",
+                              f"This string does not use correct version constraint syntax: {err}.",
+                              f.path, item.expr, "version")
+            self.m.required_providers[name] = req
+
+
+def load_module(directory: str, display_root: Optional[str] = None) -> Module:
+    """Parse every ``*.tf`` file of ``directory`` and build its Module."""
+    return _Loader(directory, display_root).load()
