@@ -16,7 +16,7 @@ from dataclasses import dataclass, field
 from typing import Optional
 
 from ..hcl import ast as A
-from ..hcl.diagnostics import Diagnostic, ERROR, WARNING
+from ..hcl.diagnostics import Diagnostic, ERROR, WARNING, has_errors
 from ..hcl.parser import parse
 from ..hcl.scanner import is_valid_identifier
 from ..hcl.tokens import Token
@@ -155,6 +155,7 @@ class Module:
     required_providers: dict[str, RequiredProvider] = field(default_factory=dict)
     required_versions: list[tuple[str, Decl]] = field(default_factory=list)
     diags: list[Diagnostic] = field(default_factory=list)
+    broken_files: set = field(default_factory=set)       # files with syntax errors
 
     def used_provider_names(self) -> dict[str, list[Resource]]:
         out: dict[str, list[Resource]] = {}
@@ -196,8 +197,13 @@ class _Loader:
             body, diags, tokens = parse(src, disp)
             self.m.diags.extend(diags)
             self.m.files.append(SourceFile(disp, src, body, tokens))
+            if has_errors(diags):
+                self.m.broken_files.add(disp)
         for f in self.m.files:
-            self.top_level(f)
+            # a file that does not parse contributes no declarations: what the
+            # recovering parser salvaged would only produce follow-on noise
+            if f.path not in self.m.broken_files:
+                self.top_level(f)
         return self.m
 
     # -- top level -----------------------------------------------------------

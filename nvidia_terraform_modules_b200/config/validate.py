@@ -90,6 +90,8 @@ class Validator:
     # -- entry ---------------------------------------------------------------
     def run(self) -> list[Diagnostic]:
         for f in self.m.files:
+            if f.path in self.m.broken_files:
+                continue
             for item in f.body.items:
                 if isinstance(item, A.Block):
                     handler = getattr(self, "visit_" + item.type, None)
@@ -574,6 +576,12 @@ def validate_module(directory: str, display_root: Optional[str] = None) -> Valid
     m = load_module(directory, display_root)
     v = Validator(m)
     diags = list(m.diags)
+    if m.broken_files:
+        # like Terraform: nothing beyond the syntax errors is reported until
+        # every file parses, since missing declarations would cascade
+        diags = [d for d in diags if d.rule == "syntax"]
+        diags.sort(key=lambda d: (d.file, d.line, d.col))
+        return ValidateResult(m, v, diags)
     diags.extend(v.run())
     diags.extend(check_tfvars(m))
     diags.sort(key=lambda d: (d.file, d.line, d.col))

@@ -1,0 +1,115 @@
+"""README tables: generation in terraform-docs' layout and drift detection."""
+from nvidia_terraform_modules_b200.config.model import load_module
+from nvidia_terraform_modules_b200.docs.tfdocs import check_readme, parse_readme, render
+
+FILES = {
+    "versions.tf": 'terraform {\n  required_version = ">= 1.2.4"\n  required_providers {\n    aws = {\n'
+                   '      source  = "hashicorp/aws"\n      version = "~>4.45.0"\n    }\n    pinned = {\n'
+                   '      source  = "Acme/pinned"\n      version = "1.2.3"\n    }\n    loose = {\n'
+                   '      source = "acme/loose"\n    }\n  }\n}\n',
+    "variables.tf": '''variable "cluster_name" {
+  type        = string
+  description = "Name of the vpc_id | cluster, see `a_b`"
+}
+variable "sizes" {
+  default = [1, 2]
+}
+// Comment used as description
+variable "vpc" {
+  type = object({
+    vpc_id     = string
+    subnet_ids = list(string)
+  })
+  default = null
+}
+variable "flag" {
+  type    = bool
+  default = true
+}
+''',
+    "main.tf": 'resource "aws_eks_thing" "a" {}\ndata "aws_ami" "l" {}\nresource "pinned_x" "p" {}\n'
+               'data "aws_b" "beta" {\n  provider = aws-beta\n}\n'
+               'module "vpc" {\n  source  = "terraform-aws-modules/vpc/aws"\n  version = "4.0.2"\n}\n'
+               'module "local" {\n  source = "../.."\n}\n',
+    "outputs.tf": '# where it lives\noutput "endpoint" {\n  value = 1\n}\noutput "ca" {\n  description = "CA data"\n'
+                  '  value = 2\n}\n',
+}
+
+
+def module(module_dir, readme=None):
+    files = dict(FILES)
+    if readme is not None:
+        files["README.md"] = readme
+    d = module_dir(files)
+    return d, load_module(d)
+
+
+def test_render_rows(module_dir):
+    _, m = module(module_dir)
+    text = render(m)
+    rows = set(text.splitlines())
+    assert '| <a name="requirement_terraform"></a> [terraform](#requirement\\_terraform) | >= 1.2.4 |' in rows
+    assert '| <a name="requirement_aws"></a> [aws](#requirement\\_aws) | ~>4.45.0 |' in rows
+    assert not any("requirement_loose" in r for r in rows)         # no constraint, no row
+    assert '| <a name="module_vpc"></a> [vpc](#module\\_vpc) | terraform-aws-modules/vpc/aws | 4.0.2 |' in rows
+    assert '| <a name="module_local"></a> [local](#module\\_local) | ../.. | n/a |' in rows
+    assert ('| [aws_eks_thing.a](https://registry.terraform.io/providers/hashicorp/aws/latest/docs/resources/eks_thing)'
+            ' | resource |') in rows
+    assert ('| [pinned_x.p](https://registry.terraform.io/providers/Acme/pinned/1.2.3/docs/resources/x) | resource |'
+            ) in rows
+    assert ('| [aws-beta_aws_b.beta](https://registry.terraform.io/providers/hashicorp/aws-beta/latest/docs/'
+            'data-sources/aws_b) | data source |') in rows
+    assert ('| <a name="input_cluster_name"></a> [cluster\\_name](#input\\_cluster\\_name) | '
+            'Name of the vpc\\_id \\| cluster, see `a_b` | `string` | n/a | yes |') in rows
+    assert ('| <a name="input_sizes"></a> [sizes](#input\\_sizes) | n/a | `list` | '
+            '<pre>[<br>  1,<br>  2<br>]</pre> | no |') in rows
+    assert ('| <a name="input_vpc"></a> [vpc](#input\\_vpc) | Comment used as description | '
+            '<pre>object({<br>    vpc_id     = string<br>    subnet_ids = list(string)<br>  })</pre> | `null` | no |'
+            ) in rows
+    assert '| <a name="output_endpoint"></a> [endpoint](#output\\_endpoint) | where it lives |' in rows
+    assert text.index("## Requirements") < text.index("## Providers") < text.index("## Modules") \
+        < text.index("## Resources") < text.index("## Inputs") < text.index("## Outputs")
+
+
+def test_generated_readme_has_no_drift(module_dir, tmp_path):
+    d, m = module(module_dir)
+    readme = tmp_path / "README.md"
+    readme.write_text("# Title\n\nprose\n\n### Requirements\n\nnot a table\n\n" + render(m))
+    assert check_readme(m, str(readme)) == []
+
+
+def test_every_kind_of_drift_is_reported(module_dir, tmp_path):
+    d, m = module(module_dir)
+    text = render(m)
+    text = text.replace("| `true` | no |", "| `false` | no |")                       # default
+    text = text.replace("| `string` | n/a | yes |", "| `number` | n/a | no |")        # type + required
+    text = text.replace("| CA data |", "| Certificate |")                             # output description
+    text = text.replace("| 4.0.2 |", "| 3.0.0 |")                                     # module version
+    text = text.replace("| >= 1.2.4 |", "| >= 1.0 |")                                 # requirement
+    lines = [ln for ln in text.splitlines() if "input_sizes" not in ln and "aws_ami.l" not in ln]
+    lines.insert(lines.index("## Inputs") + 4,
+                 '| <a name="input_ghost"></a> [ghost](#input\\_ghost) | n/a | `any` | n/a | yes |')
+    readme = tmp_path / "README.md"
+    readme.write_text("\n".join(lines) + "\n")
+    got = sorted((x.rule, x.summary.split(":")[0]) for x in check_readme(m, str(readme)))
+    assert got == [
+        ("docs-drift", 'input "cluster_name"'), ("docs-drift", 'input "cluster_name"'),
+        ("docs-drift", 'input "flag"'), ("docs-drift", 'module "vpc"'), ("docs-drift", 'output "ca"'),
+        ("docs-drift", 'requirement "terraform"'),
+        ("docs-missing-input", 'input "sizes" is not documented in the README'),
+        ("docs-missing-resource", 'data source "aws_ami.l" is not documented in the README'),
+        ("docs-unknown-input", 'README documents input "ghost" which is not declared'),
+    ]
+
+
+def test_readme_without_tables_is_not_judged(module_dir, tmp_path):
+    _, m = module(module_dir)
+    readme = tmp_path / "README.md"
+    readme.write_text("# Title\n\n## Usage\n\nprose only\n")
+    assert check_readme(m, str(readme)) == []
+
+
+def test_parse_readme_handles_escaped_pipes_and_line_numbers():
+    t = parse_readme("x\n## Inputs\n\n| Name | Description |\n|---|---|\n| a | b \\| c |\n\n## Outputs\n\nNo outputs.\n")
+    assert t["Inputs"].rows == [(6, ["a", "b | c"])]
+    assert t["Outputs"].header == []

@@ -1,0 +1,118 @@
+"""Lint rules: one positive and one negative case per rule."""
+import pytest
+
+from nvidia_terraform_modules_b200.config.validate import validate_module
+from nvidia_terraform_modules_b200.lint.rules import RULES, run_rules
+
+HEADER = ('terraform {\n  required_version = ">= 1.3"\n  required_providers {\n    aws = {\n'
+          '      source  = "hashicorp/aws"\n      version = "~> 4.0"\n    }\n  }\n}\n')
+
+
+def lint(module_dir, files, only=None):
+    res = validate_module(module_dir(files))
+    return [(d.rule, d.line) for d in run_rules(res, only={only} if only else None)]
+
+
+def rules_hit(module_dir, text, only, **more):
+    files = {"main.tf": text}
+    files.update({k.replace("__", "/").replace("_tf", ".tf"): v for k, v in more.items()})
+    return lint(module_dir, files, only)
+
+
+def test_rule_ids_are_unique_and_documented():
+    ids = [r.id for r in RULES]
+    assert len(ids) == len(set(ids)) and len(ids) >= 20
+    assert all(r.summary and r.severity in ("warning", "notice") for r in RULES)
+
+
+def test_tidy_module_has_no_findings(module_dir):
+    files = {
+        "versions.tf": HEADER,
+        "variables.tf": 'variable "name" {\n  type        = string\n  description = "n"\n}\n',
+        "main.tf": 'resource "aws_thing" "a" {\n  name = var.name\n}\n',
+        "outputs.tf": 'output "id" {\n  description = "id"\n  value       = aws_thing.a.id\n}\n',
+    }
+    assert lint(module_dir, files) == []
+
+
+@pytest.mark.parametrize("rule,text,lines", [
+    ("unused-variable", 'variable "a" {}\nvariable "b" {}\noutput "o" {\n  value = var.a\n}\n', [2]),
+    ("unused-local", 'locals {\n  a = 1\n  b = local.a\n}\n', [3]),
+    ("unused-data-source", 'data "aws_a" "x" {}\ndata "aws_a" "y" {}\noutput "o" {\n  value = data.aws_a.x.id\n}\n', [2]),
+    ("module-unpinned", 'module "a" {\n  source = "ns/n/aws"\n}\nmodule "b" {\n  source  = "ns/n/aws"\n'
+                        '  version = "1.0.0"\n}\nmodule "c" {\n  source = "git::https://x/y.git"\n}\n'
+                        'module "d" {\n  source = "git::https://x/y.git?ref=v1"\n}\n', [1, 8]),
+    ("required-provider-missing", HEADER + 'resource "aws_a" "x" {}\nresource "helm_release" "y" {}\n'
+                                           'provider "kubernetes" {}\n', [11, 12]),
+    ("required-provider-unused", HEADER + 'resource "null_resource" "x" {}\n', [4]),
+    ("provider-version-missing", 'terraform {\n  required_providers {\n    aws = {\n      source = "hashicorp/aws"\n'
+                                 '    }\n  }\n}\n', [3]),
+    ("required-version-missing", 'resource "aws_a" "x" {}\n', [1]),
+    ("undocumented", 'variable "a" {}\nvariable "b" {\n  description = "d"\n}\noutput "o" {\n  value = 1\n}\n', [1, 5]),
+    ("untyped-variable", 'variable "a" {}\nvariable "b" {\n  type = string\n}\n', [1]),
+    ("naming-convention", 'resource "aws_a" "my-thing" {}\nresource "aws_a" "my_thing" {}\n'
+                          'variable "Upper" {}\n', [1, 3]),
+    ("deprecated-index", 'output "o" {\n  value = [aws_a.x.list.0.id, aws_a.x.list[0].id]\n}\nresource "aws_a" "x" {}\n',
+     [2]),
+    ("legacy-splat", 'resource "aws_a" "x" {\n  count = 1\n}\noutput "o" {\n  value = [aws_a.x.*.id, aws_a.x[*].id]\n}\n',
+     [5]),
+    ("comment-syntax", '// old style\n# new style\n/* block */\nlocals {}\n', [1]),
+    ("length-of-object", 'data "aws_a" "x" {}\ndata "aws_a" "n" {\n  count = 2\n}\nlocals {\n'
+                         '  bad  = length(data.aws_a.x)\n  ok1  = length(data.aws_a.x.ids)\n'
+                         '  ok2  = length(data.aws_a.n)\n}\n', [6]),
+    ("duplicate-resource-arguments",
+     'variable "r" {}\nresource "aws_att" "gpu" {\n  role = var.r\n  arn  = "a"\n}\n'
+     'resource "aws_att" "cpu" {\n  role = var.r\n  arn  = "a"\n}\n'
+     'resource "aws_att" "other" {\n  role = var.r\n  arn  = "b"\n}\n', [6]),
+    ("guard-mismatch",
+     'variable "a" {}\nvariable "b" {}\nresource "aws_r" "x" {\n  count = var.a ? 1 : 0\n}\n'
+     'output "bad" {\n  value = var.b == false ? null : aws_r.x[0].arn\n}\n'
+     'output "good" {\n  value = var.a ? aws_r.x[0].arn : null\n}\n', [7]),
+    ("secret-in-command",
+     'data "az_ws" "w" {}\nresource "null_resource" "n" {\n  provisioner "local-exec" {\n'
+     '    command = "kubectl create secret --from-literal=K=${data.az_ws.w.primary_shared_key} '
+     '--id=${data.az_ws.w.workspace_id}"\n  }\n}\n', [4]),
+    ("local-exec", 'resource "null_resource" "n" {\n  provisioner "local-exec" {\n    command = "helm repo add x y"\n'
+                   '  }\n}\n', [2]),
+])
+def test_rule(module_dir, rule, text, lines):
+    assert rules_hit(module_dir, text, rule) == [(rule, ln) for ln in lines]
+
+
+def test_standard_module_structure(module_dir):
+    hits = lint(module_dir, {"main.tf": 'variable "a" {}\n', "output.tf": 'output "o" {\n  value = 1\n}\n'},
+                "standard-module-structure")
+    # variables.tf and outputs.tf missing; one variable and one output misplaced
+    assert len(hits) == 4
+
+
+def test_eof_newline_includes_tfvars(module_dir):
+    hits = lint(module_dir, {"main.tf": "locals {}", "ok.tf": "locals {}\n", "terraform.tfvars": "# c"},
+                "eof-newline")
+    assert hits == [("eof-newline", 1), ("eof-newline", 1)]
+
+
+def test_provider_in_called_module(module_dir):
+    files = {
+        "main.tf": 'module "c" {\n  source = "./c"\n}\nmodule "d" {\n  source = "./d"\n  count  = 1\n}\n'
+                   'module "e" {\n  source = "./e"\n}\n',
+        "c/main.tf": 'provider "helm" {}\n',
+        "d/main.tf": 'provider "helm" {}\n',
+        "e/main.tf": 'locals {}\n',
+    }
+    res = validate_module(module_dir(files))
+    found = [(d.severity, d.line) for d in run_rules(res, only={"provider-in-module"})]
+    assert found == [("notice", 1), ("warning", 4)]
+
+
+def test_unused_provider_passed_to_child_is_used(module_dir):
+    text = HEADER + 'module "c" {\n  source = "./c"\n  providers = {\n    aws = aws\n  }\n}\n'
+    assert rules_hit(module_dir, text, "required-provider-unused", c__main_tf="") == []
+
+
+def test_only_and_skip(module_dir):
+    res = validate_module(module_dir({"main.tf": '// c\nvariable "a" {}\n'}))
+    everything = {d.rule for d in run_rules(res)}
+    assert {"comment-syntax", "unused-variable"} <= everything
+    assert {d.rule for d in run_rules(res, only={"comment-syntax"})} == {"comment-syntax"}
+    assert "comment-syntax" not in {d.rule for d in run_rules(res, skip={"comment-syntax"})}

@@ -1,0 +1,310 @@
+"""validate: structural rules of the configuration loader and reference checks.
+Each case is a tiny module written for the test; messages are compared with
+Terraform's wording."""
+import pytest
+
+from nvidia_terraform_modules_b200.config.validate import validate_module
+
+
+def diag_set(module_dir, files):
+    res = validate_module(module_dir(files))
+    return res, [(d.severity, d.summary) for d in res.diags]
+
+
+def summaries(module_dir, text, **more):
+    files = {"main.tf": text}
+    files.update(more)
+    return [s for _, s in diag_set(module_dir, files)[1]]
+
+
+GOOD = {
+    "versions.tf": 'terraform {\n  required_version = ">= 1.3"\n  required_providers {\n'
+                   '    aws = {\n      source  = "hashicorp/aws"\n      version = "~> 4.0"\n    }\n  }\n}\n',
+    "variables.tf": 'variable "name" {\n  type = string\n}\nvariable "on" {\n  type    = bool\n  default = true\n}\n'
+                    'variable "zones" {\n  type    = list(string)\n  default = []\n}\n',
+    "main.tf": '''
+locals {
+  tags = { for z in var.zones : z => upper(z) }
+}
+resource "aws_thing" "many" {
+  count = var.on ? 1 : 0
+  name  = "${var.name}-${count.index}"
+  tags  = local.tags
+}
+resource "aws_thing" "each" {
+  for_each = toset(var.zones)
+  name     = each.key
+  peer     = aws_thing.many[0].id
+  dynamic "rule" {
+    for_each = var.zones
+    iterator = it
+    content {
+      zone = it.value
+      all  = aws_thing.many[*].id
+    }
+  }
+  provisioner "local-exec" {
+    command = "echo ${self.id} ${path.module} ${terraform.workspace}"
+  }
+  lifecycle {
+    ignore_changes = [tags]
+  }
+  depends_on = [aws_thing.many, data.aws_zone.z]
+}
+data "aws_zone" "z" {
+  name = one(aws_thing.many[*].name)
+}
+module "child" {
+  source = "./child"
+  label  = var.name
+}
+output "ids" {
+  value = [for k, t in aws_thing.each : t.id if k != ""]
+}
+output "child" {
+  value = module.child.out
+}
+''',
+    "child/main.tf": 'variable "label" {\n  type = string\n}\nvariable "opt" {\n  default = 1\n}\n'
+                     'output "out" {\n  value = var.label\n}\n',
+}
+
+
+def test_well_formed_module_is_valid(module_dir):
+    res, diags = diag_set(module_dir, GOOD)
+    assert diags == [] and res.valid
+    assert res.validator.used_vars == {"name", "on", "zones"}
+    assert res.validator.used_locals == {"tags"}
+
+
+# ------------------------------------------------------------- references
+@pytest.mark.parametrize("expr,summary", [
+    ("var.nope", "Reference to undeclared input variable"),
+    ("local.nope", "Reference to undeclared local value"),
+    ("module.nope.x", "Reference to undeclared module"),
+    ("aws_x.nope.id", "Reference to undeclared resource"),
+    ("data.aws_x.nope.id", "Reference to undeclared resource"),
+    ("var", "Invalid reference"),
+    ("aws_x", "Invalid reference"),
+    ("data.aws_x", "Invalid reference"),
+    ("count.index", 'Reference to "count" in non-counted context'),
+    ("each.key", 'Reference to "each" in context without for_each'),
+    ("self.id", 'Invalid "self" reference'),
+    ("path.nowhere", 'Invalid "path" attribute'),
+    ("terraform.version", 'Invalid "terraform" attribute'),
+    ("uppercase(\"a\")", "Call to unknown function"),
+    ("length()", "Not enough function arguments"),
+    ("list(1, 2)", "Error in function call"),
+    ("[for x in [1] : y]", "Invalid reference"),
+])
+def test_reference_errors(module_dir, expr, summary):
+    got = summaries(module_dir, f'output "o" {{\n  value = {expr}\n}}\n')
+    assert got == [summary]
+
+
+def test_for_and_dynamic_names_are_scoped(module_dir):
+    text = '''
+resource "aws_a" "b" {
+  dynamic "rule" {
+    for_each = [1]
+    content {
+      v = rule.value
+    }
+  }
+  leak = rule.value
+}
+'''
+    # outside the content block "rule" is just an (undeclared) resource type
+    assert summaries(module_dir, text) == ["Reference to undeclared resource"]
+
+
+def test_count_and_each_contexts(module_dir):
+    text = '''
+resource "aws_a" "counted" {
+  count = 2
+  i     = count.index
+  bad   = count.total
+  worse = each.key
+}
+resource "aws_a" "plain" {
+  i = count.index
+}
+resource "aws_a" "self_count" {
+  count = count.index
+}
+'''
+    assert summaries(module_dir, text) == ['Invalid "count" attribute',
+                                           'Reference to "each" in context without for_each',
+                                           'Reference to "count" in non-counted context',
+                                           'Reference to "count" in non-counted context']
+
+
+def test_instance_keys_must_match_count(module_dir):
+    text = '''
+resource "aws_a" "one" {}
+resource "aws_a" "many" {
+  count = 2
+}
+output "a" {
+  value = aws_a.one[0].id
+}
+output "b" {
+  value = aws_a.many.id
+}
+output "c" {
+  value = [aws_a.one.id, aws_a.many[0].id, aws_a.many[*].id, aws_a.many, length(aws_a.many)]
+}
+output "d" {
+  value = aws_a.one[count.index]
+}
+'''
+    assert summaries(module_dir, text) == ["Unexpected resource instance key", "Missing resource instance key",
+                                           "Unexpected resource instance key",
+                                           'Reference to "count" in non-counted context']
+
+
+def test_module_instance_keys_and_outputs(module_dir):
+    files = {
+        "main.tf": '''
+module "one" {
+  source = "./c"
+  need   = 1
+}
+module "many" {
+  source = "./c"
+  count  = 2
+  need   = count.index
+}
+output "a" {
+  value = [module.one.out, module.many[0].out, module.many.*.out, module.many[*].out]
+}
+output "b" {
+  value = module.one[0].out
+}
+output "c" {
+  value = module.many.out
+}
+output "d" {
+  value = module.one.missing
+}
+''',
+        "c/main.tf": 'variable "need" {}\noutput "out" {\n  value = var.need\n}\n',
+    }
+    _, diags = diag_set(module_dir, files)
+    assert [s for _, s in diags] == ["Unexpected module instance key", "Missing module instance key",
+                                     "Unsupported attribute"]
+
+
+def test_local_module_call_arguments(module_dir):
+    files = {
+        "main.tf": 'module "m" {\n  source = "./c"\n  extra  = 1\n}\n'
+                   'module "gone" {\n  source = "./missing"\n}\n'
+                   'module "remote" {\n  source  = "ns/name/aws"\n  version = "1.0.0"\n  anything = 1\n}\n',
+        "c/main.tf": 'variable "need" {}\nvariable "opt" {\n  default = 1\n}\n',
+    }
+    _, diags = diag_set(module_dir, files)
+    assert sorted(s for _, s in diags) == ["Missing required argument", "Unreadable module directory",
+                                           "Unsupported argument"]
+
+
+def test_depends_on_must_be_static_references(module_dir):
+    text = '''
+resource "aws_a" "b" {}
+resource "aws_a" "c" {
+  depends_on = [aws_a.b, "aws_a.b", upper("x"), aws_a.nope]
+}
+resource "aws_a" "d" {
+  depends_on = aws_a.b
+}
+'''
+    assert summaries(module_dir, text) == ["Quoted references are deprecated", "Invalid expression",
+                                           "Reference to undeclared resource", "Invalid expression"]
+
+
+def test_deprecation_warnings_do_not_make_a_module_invalid(module_dir):
+    res, diags = diag_set(module_dir, {"main.tf": 'variable "a" {}\noutput "o" {\n  value = "${var.a}"\n}\n'
+                                                  'provider "aws" {\n  version = "~> 4.0"\n}\n'})
+    assert diags == [("warning", "Interpolation-only expressions are deprecated"),
+                     ("warning", "Version constraints inside provider configuration blocks are deprecated")]
+    assert res.valid
+
+
+# --------------------------------------------------------------- structure
+@pytest.mark.parametrize("text,summary", [
+    ("x = 1\n", "Unsupported argument"),
+    ("frob {}\n", "Unsupported block type"),
+    ('resource "a" {}\n', "Missing name for resource"),
+    ("resource {}\n", "Missing type for resource"),
+    ('variable "a" "b" {}\n', "Extraneous label for variable"),
+    ('locals "x" {}\n', "Extraneous label for locals"),
+    ('resource "9a" "b" {}\n', "Invalid resource type name"),
+    ('variable "count" {}\n', "Invalid variable name"),
+    ('variable "a" {\n  typ = string\n}\n', "Unsupported argument"),
+    ('variable "a" {\n  type = strng\n}\n', "Invalid type specification"),
+    ('variable "a" {\n  type = "string"\n}\n', "Invalid type specification"),
+    ('variable "a" {\n  type    = number\n  default = "x"\n}\n', "Invalid default value for variable"),
+    ('variable "a" {\n  type    = string\n  default = var.b\n}\n', "Variables not allowed"),
+    ('variable "a" {\n  default  = null\n  nullable = false\n}\n', "Invalid default value for variable"),
+    ('variable "a" {}\nvariable "a" {}\n', "Duplicate variable declaration"),
+    ('output "a" {}\n', "Missing required argument"),
+    ('output "a" {\n  value = 1\n}\noutput "a" {\n  value = 2\n}\n', "Duplicate output definition"),
+    ('locals {\n  a = 1\n}\nlocals {\n  a = 2\n}\n', "Duplicate local value definition"),
+    ('resource "a_b" "c" {}\nresource "a_b" "c" {}\n', 'Duplicate resource "a_b" configuration'),
+    ('data "a_b" "c" {}\ndata "a_b" "c" {}\n', 'Duplicate data "a_b" configuration'),
+    ('module "m" {}\n', "Missing required argument"),
+    ('module "m" {\n  source = "a/b/c"\n  version = "one"\n}\n', "Invalid version constraint"),
+    ('module "m" {\n  source = var.s\n}\nvariable "s" {}\n', "Variables not allowed"),
+    ('resource "a_b" "c" {\n  count    = 1\n  for_each = {}\n}\n', 'Invalid combination of "count" and "for_each"'),
+    ('resource "a_b" "c" {\n  provider = 1 + 1\n}\n', "Invalid provider configuration reference"),
+    ('resource "a_b" "c" {\n  lifecycle {\n    frob = 1\n  }\n}\n', "Unsupported argument"),
+    ('data "a_b" "c" {\n  provisioner "x" {}\n}\n', "Data resources do not have provisioners"),
+    ('resource "a_b" "c" {\n  dynamic "x" {\n    content {}\n  }\n}\n', "Missing required argument"),
+    ('resource "a_b" "c" {\n  dynamic "x" {\n    for_each = []\n  }\n}\n', "Insufficient content blocks"),
+    ('provider "aws" {}\nprovider "aws" {}\n', "Duplicate provider configuration"),
+    ('provider "aws" {\n  alias = "9x"\n}\n', "Invalid provider configuration alias"),
+    ('terraform {\n  required_version = ">> 1"\n}\n', "Invalid version constraint"),
+    ('terraform {\n  frob = 1\n}\n', "Unsupported argument"),
+    ('terraform {\n  required_providers {\n    aws = {\n      sauce = "x"\n    }\n  }\n}\n',
+     "Invalid required_providers object"),
+    ('terraform {\n  required_providers {\n    aws = {\n      source = "a/b/c/d"\n    }\n  }\n}\n',
+     "Invalid provider source string"),
+    ('terraform {\n  required_providers {\n    aws = "~> 4.0"\n    aws = "~> 5.0"\n  }\n}\n',
+     "Duplicate required providers configuration"),
+    ('resource "a_b" "c" {\n  x = 1\n  x = 2\n}\n', None),    # body arguments need the provider schema
+])
+def test_structural_errors(module_dir, text, summary):
+    got = summaries(module_dir, text)
+    assert got == ([summary] if summary else [])
+
+
+def test_version_is_only_for_registry_sources(module_dir):
+    _, diags = diag_set(module_dir, {"main.tf": 'module "m" {\n  source  = "./x"\n  version = "1.0"\n}\n',
+                                     "x/main.tf": ""})
+    assert [s for _, s in diags] == ["Invalid registry module source address"]
+
+
+def test_aliased_providers_are_distinct(module_dir):
+    assert summaries(module_dir, 'provider "aws" {}\nprovider "aws" {\n  alias = "west"\n}\n'
+                                 'resource "aws_a" "b" {\n  provider = aws.west\n}\n') == []
+
+
+def test_syntax_errors_are_reported_with_file_names(module_dir):
+    res, _ = diag_set(module_dir, {"main.tf": 'output "a" {\n  value = (\n}\n', "ok.tf": 'variable "v" {}\n'})
+    assert not res.valid
+    assert [(d.rule, d.summary) for d in res.diags] == [("syntax", "Invalid expression")]
+    assert res.diags[0].file.endswith("main.tf")
+    assert "v" in res.module.variables          # the healthy file was still loaded
+    assert "a" not in res.module.outputs        # nothing is salvaged from the broken one
+
+
+# ------------------------------------------------------------------ tfvars
+def test_tfvars_are_checked_against_declarations(module_dir):
+    files = {
+        "main.tf": 'variable "n" {\n  type = number\n}\nvariable "s" {\n  type = string\n}\n',
+        "terraform.tfvars": 'n = "many"\ns = var.n\nghost = 1\n',
+        "extra.auto.tfvars": 'blk {}\n',
+        "ignored.tfvars": 'ghost2 = 1\n',
+    }
+    res, diags = diag_set(module_dir, files)
+    assert sorted(s for _, s in diags) == ["Invalid value for input variable", "Unexpected block",
+                                           "Value for undeclared variable", "Variables not allowed"]
