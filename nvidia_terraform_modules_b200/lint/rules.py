@@ -422,6 +422,67 @@ def secret_in_command(c: LintContext):
                                      "file instead.", r.file, ref)
 
 
+_PAIRS = (("cpu", "gpu"), ("public", "private"), ("primary", "secondary"), ("source", "destination"),
+          ("ingress", "egress"), ("blue", "green"), ("reader", "writer"))
+
+
+def _tokens(name: str) -> set[str]:
+    return set(re.split(r"[_\-.]+", name.lower()))
+
+
+def _sides(name: str) -> set[tuple[int, int]]:
+    """(pair index, side) for each pair of which ``name`` carries exactly one side."""
+    toks = _tokens(name)
+    out = set()
+    for i, (a, b) in enumerate(_PAIRS):
+        if (a in toks) != (b in toks):
+            out.add((i, 0 if a in toks else 1))
+    return out
+
+
+def _opposites(owner: str, subtree: A.Node) -> Iterator[tuple[A.ScopeTraversal, str, str]]:
+    mine = _sides(owner)
+    if not mine:
+        return
+    for ref in subtree.walk():
+        if not isinstance(ref, A.ScopeTraversal):
+            continue
+        for step in ref.steps:
+            if step.kind != "attr":
+                continue
+            for (i, side) in _sides(str(step.value)):
+                if (i, 1 - side) in mine:
+                    yield ref, _PAIRS[i][1 - side], _PAIRS[i][side]
+                    break
+            else:
+                continue
+            break
+
+
+@rule("counterpart-mismatch", NOTICE, "a cpu/gpu (public/private, ...) block refers to its counterpart's value")
+def counterpart_mismatch(c: LintContext):
+    def note(file: str, owner: str, kind: str, ref: A.ScopeTraversal, own: str, other: str):
+        return _d("counterpart-mismatch", NOTICE,
+                  f"{kind} \"{owner}\" is the {own} one but reads {ref.dotted()}",
+                  f"Names pair up as {own}/{other}; a {own} block reading a {other} value is often a copy-paste "
+                  "slip. Ignore if intended.", file, ref)
+    for r in c.m.resources.values():
+        if r.block is not None:
+            for ref, own, other in _opposites(r.name, r.block.body):
+                yield note(r.file, r.name, "data source" if r.mode == "data" else "resource", ref, own, other)
+    for name, o in c.m.outputs.items():
+        if o.block is not None:
+            for ref, own, other in _opposites(name, o.block.body):
+                yield note(o.file, name, "output", ref, own, other)
+    for file, node in _all_exprs(c.m):
+        if isinstance(node, A.ObjectCons):
+            for key, value in node.items:
+                k = key.literal_key()
+                if k:
+                    for ref, own, other in _opposites(k, value):
+                        yield note(file, k, "object key", ref, own, other)
+
+
 @rule("provider-in-module", NOTICE, "provider configuration inside a module that other modules call")
 def provider_in_module(c: LintContext):
     # A module with its own provider blocks cannot be used with count, for_each

@@ -72,6 +72,11 @@ def test_tidy_module_has_no_findings(module_dir):
      'data "az_ws" "w" {}\nresource "null_resource" "n" {\n  provisioner "local-exec" {\n'
      '    command = "kubectl create secret --from-literal=K=${data.az_ws.w.primary_shared_key} '
      '--id=${data.az_ws.w.workspace_id}"\n  }\n}\n', [4]),
+    ("counterpart-mismatch",
+     'variable "gpu_tags" {}\nvariable "cpu_tags" {}\nresource "x_pool" "cpu_nodes" {\n  tags = var.gpu_tags\n}\n'
+     'resource "x_pool" "gpu_nodes" {\n  tags = var.gpu_tags\n}\nresource "x_pool" "both_cpu_gpu" {\n'
+     '  tags = var.gpu_tags\n}\nlocals {\n  pools = {\n    cpu_pool = { t = var.cpu_tags }\n'
+     '    private-a = { t = var.public_x }\n  }\n}\nvariable "public_x" {}\n', [4, 15]),
     ("local-exec", 'resource "null_resource" "n" {\n  provisioner "local-exec" {\n    command = "helm repo add x y"\n'
                    '  }\n}\n', [2]),
 ])

@@ -51,6 +51,8 @@ ACCEPTANCE = [
     ("aks", "unused-variable", "aks/variables.tf", 82),         # gpu_os_sku
     ("aks", "required-provider-unused", "aks/versions.tf", 10),
     ("gke", "unused-data-source", "gke/data.tf", 4),
+    ("gke", "counterpart-mismatch", "gke/main.tf", 83),         # CPU pool tagged with gpu_instance_tags
+    ("eks/examples/cnpack", "counterpart-mismatch", "eks/examples/cnpack/aws-fluentbit.tf", 24),
     ("gke", "required-provider-missing", "gke/main.tf", 195),   # helm
     ("gke", "required-provider-missing", "gke/main.tf", 156),   # kubernetes
     ("eks/examples/cnpack", "duplicate-resource-arguments", "eks/examples/cnpack/aws-fluentbit.tf", 22),
