@@ -72,7 +72,7 @@ def main() -> int:
                            "all absent (BASELINE.md section 2)"}))
         return 0
 
-    from nvidia_terraform_modules_b200.check import STAND_IN, check_tree
+    from nvidia_terraform_modules_b200.check import STAND_IN, check_tree, clear_caches
     from nvidia_terraform_modules_b200.synth import write_tree
 
     workdir = tempfile.mkdtemp(prefix="tfbench_")
@@ -81,9 +81,11 @@ def main() -> int:
         warmup = max(args.warmup, 3)
         rep = None
         for _ in range(warmup):
+            clear_caches()
             rep = check_tree(workdir)
         t0 = time.perf_counter()
         for _ in range(args.steps):
+            clear_caches()          # every step re-reads and re-parses every file: no work is skipped
             rep = check_tree(workdir)
         dt = time.perf_counter() - t0
         ms_per_step = dt / args.steps * 1e3

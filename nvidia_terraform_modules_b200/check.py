@@ -25,6 +25,16 @@ STAND_IN = ("stand-in: restated from the published behaviour of Terraform / hash
             "the real `terraform` binary is not available offline, parity is unpinned")
 
 
+def clear_caches() -> None:
+    """Forget every remembered parse and module.  Within one ``check_tree`` run
+    the stages share parses; a benchmark that repeats runs must call this
+    between them, or later runs would skip the parsing work."""
+    from .config import model
+    from .hcl import parser
+    parser._FILE_CACHE.clear()
+    model._MODULE_CACHE.clear()
+
+
 def discover_modules(root: str) -> list[str]:
     """Directories under ``root`` (hidden ones skipped) holding ``*.tf`` files,
     relative to ``root``, parents before children."""

@@ -17,7 +17,7 @@ from typing import Optional
 
 from ..hcl import ast as A
 from ..hcl.diagnostics import Diagnostic, ERROR, WARNING, has_errors
-from ..hcl.parser import parse
+from ..hcl.parser import parse_path
 from ..hcl.scanner import is_valid_identifier
 from ..hcl.tokens import Token
 from . import typeexpr
@@ -156,6 +156,7 @@ class Module:
     required_versions: list[tuple[str, Decl]] = field(default_factory=list)
     diags: list[Diagnostic] = field(default_factory=list)
     broken_files: set = field(default_factory=set)       # files with syntax errors
+    display_root: Optional[str] = None                   # paths in messages are relative to this
 
     def used_provider_names(self) -> dict[str, list[Resource]]:
         out: dict[str, list[Resource]] = {}
@@ -168,6 +169,7 @@ class Module:
 class _Loader:
     def __init__(self, directory: str, display_root: Optional[str] = None):
         self.m = Module(directory)
+        self.m.display_root = display_root
         self.root = display_root
 
     def diag(self, sev: str, summary: str, detail: str, file: str, node, rule: str) -> None:
@@ -191,10 +193,8 @@ class _Loader:
         tf = [n for n in names if n.endswith(".tf") and not n.startswith((".", "~", "#"))]
         for name in tf:
             path = os.path.join(self.m.dir, name)
-            with open(path, "r", encoding="utf-8", newline="") as fh:
-                src = fh.read()
             disp = self.display(path)
-            body, diags, tokens = parse(src, disp)
+            src, body, diags, tokens = parse_path(path, disp)
             self.m.diags.extend(diags)
             self.m.files.append(SourceFile(disp, src, body, tokens))
             if has_errors(diags):
@@ -619,6 +619,28 @@ class _Loader:
             self.m.required_providers[name] = req
 
 
+_MODULE_CACHE: dict[tuple, Module] = {}
+
+
+def _signature(directory: str) -> tuple:
+    try:
+        names = sorted(n for n in os.listdir(directory) if n.endswith(".tf"))
+    except OSError:
+        return ()
+    sig = []
+    for n in names:
+        st = os.stat(os.path.join(directory, n))
+        sig.append((n, st.st_mtime_ns, st.st_size))
+    return tuple(sig)
+
+
 def load_module(directory: str, display_root: Optional[str] = None) -> Module:
-    """Parse every ``*.tf`` file of ``directory`` and build its Module."""
-    return _Loader(directory, display_root).load()
+    """Parse every ``*.tf`` file of ``directory`` and build its Module.  The
+    result is shared (and must be treated as read-only) until a file changes."""
+    key = (os.path.abspath(directory), display_root, _signature(directory))
+    m = _MODULE_CACHE.get(key)
+    if m is None:
+        if len(_MODULE_CACHE) > 1024:
+            _MODULE_CACHE.clear()
+        m = _MODULE_CACHE[key] = _Loader(directory, display_root).load()
+    return m

@@ -84,7 +84,7 @@ class Validator:
             return None
         if mc.name not in self.children:
             path = os.path.normpath(os.path.join(self.m.dir, mc.source))
-            self.children[mc.name] = load_module(path) if os.path.isdir(path) else None
+            self.children[mc.name] = load_module(path, self.m.display_root) if os.path.isdir(path) else None
         return self.children[mc.name]
 
     # -- entry ---------------------------------------------------------------

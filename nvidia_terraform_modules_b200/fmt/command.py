@@ -26,7 +26,7 @@ from dataclasses import dataclass, field
 from typing import Iterable, TextIO
 
 from ..hcl.diagnostics import Diagnostic, has_errors
-from ..hcl.parser import parse
+from ..hcl.parser import parse, parse_path
 from ..hcl.tokens import render
 from .canonical import format_tokens
 from .rewrites import apply_rewrites, collect_rewrites
@@ -34,15 +34,22 @@ from .rewrites import apply_rewrites, collect_rewrites
 FMT_SUFFIXES = (".tf", ".tfvars", ".tftest.hcl")
 
 
-def format_source(src: str, filename: str = "") -> tuple[str, list[Diagnostic]]:
+def format_source(src: str, filename: str = "", parsed=None) -> tuple[str, list[Diagnostic]]:
     """Canonical form of one file's text.  On syntax errors the text is
-    returned unchanged together with the diagnostics."""
-    body, diags, tokens = parse(src, filename)
+    returned unchanged together with the diagnostics.  ``parsed`` may hand in
+    an existing ``(body, diagnostics, tokens)`` for ``src``; its tokens are
+    left exactly as they were."""
+    body, diags, tokens = parsed if parsed is not None else parse(src, filename)
     if has_errors(diags):
         return src, diags
-    tokens = apply_rewrites(tokens, collect_rewrites(body, tokens))
-    format_tokens(tokens)
-    out = render(tokens)
+    saved = [t.spaces_before for t in tokens]
+    try:
+        laid_out = apply_rewrites(tokens, collect_rewrites(body, tokens))
+        format_tokens(laid_out)
+        out = render(laid_out)
+    finally:
+        for t, n in zip(tokens, saved):
+            t.spaces_before = n
     if src.startswith("\ufeff"):
         out = "\ufeff" + out
     return out, diags
@@ -134,11 +141,10 @@ def run_fmt(targets: Iterable[str], *, recursive: bool = False, write: bool = Tr
             res.diags.append(Diagnostic("error", f"No file or directory at {target}", file=target,
                                         rule="fmt-target"))
     for path in files:
-        with open(path, "r", encoding="utf-8", newline="") as fh:
-            src = fh.read()
+        src, body, pdiags, tokens = parse_path(path, _display(path))
         res.checked.append(_display(path))
         res.bytes_checked += len(src.encode("utf-8"))
-        out, diags = format_source(src, _display(path))
+        out, diags = format_source(src, _display(path), (body, pdiags, tokens))
         res.diags.extend(diags)
         if has_errors(diags) or out == src:
             continue

@@ -12,6 +12,7 @@ a maintainer will compare messages.
 """
 from __future__ import annotations
 
+import os
 from typing import Optional
 
 from . import ast as A
@@ -27,6 +28,8 @@ _BINARY_LEVELS: list[dict[T, str]] = [
     {T.PLUS: "+", T.MINUS: "-"},
     {T.STAR: "*", T.SLASH: "/", T.PERCENT: "%"},
 ]
+
+_PRECEDENCE: dict[T, int] = {typ: level for level, ops in enumerate(_BINARY_LEVELS) for typ in ops}
 
 _ESCAPES = {"n": "\n", "r": "\r", "t": "\t", '"': '"', "\\": "\\"}
 
@@ -129,12 +132,16 @@ class Parser:
             raise self.error(summary, detail, tok)
         return self.next()
 
-    def _mark(self) -> tuple[int, A.Pos]:
-        tok = self.peek()
-        return self._full_index(), A.Pos(tok.line, tok.col)
+    def _mark(self) -> int:
+        """Parser position of the next significant token (cheap: positions are
+        only turned into line/column when a node is actually finished)."""
+        self._skip_nl()
+        return self.p
 
-    def _finish(self, node, mark):
-        node.tok_start, node.pos = mark
+    def _finish(self, node, mark: int):
+        tok = self.toks[mark]
+        node.tok_start = self.idx[mark]
+        node.pos = A.Pos(tok.line, tok.col)
         # end = full index just past the last consumed parser token
         node.tok_end = self.idx[self.p - 1] + 1 if self.p > 0 else 0
         return node
@@ -320,6 +327,8 @@ class Parser:
     def parse_expr(self) -> A.Expr:
         mark = self._mark()
         cond = self._binary(0)
+        if self.toks[self.p].type is not T.QUESTION and not self._nl_ignore[-1]:
+            return cond                  # common case: nothing follows on this line
         if self.peek().type is T.QUESTION:
             self.next()
             t = self.parse_expr()
@@ -333,17 +342,18 @@ class Parser:
             return self._finish(A.Conditional(cond, t, f), mark)
         return cond
 
-    def _binary(self, level: int) -> A.Expr:
-        if level == len(_BINARY_LEVELS):
-            return self._unary()
+    def _binary(self, min_prec: int) -> A.Expr:
+        """Precedence climbing over the six binary operator levels."""
         mark = self._mark()
-        ops = _BINARY_LEVELS[level]
-        lhs = self._binary(level + 1)
-        while self.peek().type in ops:
-            op = ops[self.next().type]
-            rhs = self._binary(level + 1)
-            lhs = self._finish(A.Binary(op, lhs, rhs), mark)
-        return lhs
+        lhs = self._unary()
+        while True:
+            tok = self.peek()
+            prec = _PRECEDENCE.get(tok.type)
+            if prec is None or prec < min_prec:
+                return lhs
+            self.next()
+            rhs = self._binary(prec + 1)
+            lhs = self._finish(A.Binary(tok.text, lhs, rhs), mark)
 
     def _unary(self) -> A.Expr:
         tok = self.peek()
@@ -883,3 +893,25 @@ def parse(src: str, filename: str = "") -> tuple[A.Body, list[Diagnostic], list[
     parser = Parser(src, filename)
     body = parser.parse_file()
     return body, parser.diags, parser.all
+
+
+_FILE_CACHE: dict[tuple, tuple[str, A.Body, list[Diagnostic], list[Token]]] = {}
+
+
+def parse_path(path: str, display: str) -> tuple[str, A.Body, list[Diagnostic], list[Token]]:
+    """Read and parse a file, remembering the result until the file changes
+    (size or modification time).  One ``check`` run looks at each file several
+    times -- fmt, the module that owns it, modules that call that module -- and
+    they all share one parse.  Callers must treat the result as read-only;
+    ``fmt`` restores the ``spaces_before`` values it touches."""
+    st = os.stat(path)
+    key = (os.path.abspath(path), display, st.st_mtime_ns, st.st_size)
+    hit = _FILE_CACHE.get(key)
+    if hit is None:
+        with open(path, "r", encoding="utf-8", newline="") as fh:
+            src = fh.read()
+        body, diags, tokens = parse(src, display)
+        if len(_FILE_CACHE) > 4096:
+            _FILE_CACHE.clear()
+        hit = _FILE_CACHE[key] = (src, body, diags, tokens)
+    return hit

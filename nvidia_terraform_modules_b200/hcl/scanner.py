@@ -18,6 +18,7 @@ A ``${``/``%{`` sequence re-enters normal mode until the brace that balances it.
 """
 from __future__ import annotations
 
+import re
 import unicodedata
 
 from .tokens import T, Token
@@ -53,6 +54,18 @@ _ONE_CHAR = {
     "?": T.QUESTION,
     ":": T.COLON,
 }
+
+
+_NORMAL_RE = re.compile(r"""
+      (?P<ws>[ \t]+)
+    | (?P<ident>[A-Za-z_][A-Za-z0-9_\-]*)
+    | (?P<nl>\r?\n)
+    | (?P<comment>(?:\#|//)[^\n]*\n? | /\*.*?\*/)
+    | (?P<num>[0-9]+(?:\.[0-9]+)?(?:[eE][+-]?[0-9]+)?)
+    | (?P<dots>\.\.\.)
+    | (?P<op2>==|!=|<=|>=|&&|\|\||=>|::)
+    | (?P<op1>[\[\]()*+\-%=>!.,?:] | /(?!\*))
+""", re.VERBOSE | re.DOTALL)
 
 
 def is_id_start(ch: str) -> bool:
@@ -93,9 +106,8 @@ class Scanner:
         return self.src[i] if i < self.n else ""
 
     def _advance(self, text: str) -> None:
-        nl = text.count("\n")
-        if nl:
-            self.line += nl
+        if "\n" in text:
+            self.line += text.count("\n")
             self.col = len(text) - text.rfind("\n")
         else:
             self.col += len(text)
@@ -124,79 +136,77 @@ class Scanner:
 
     # -- normal mode -------------------------------------------------------
     def _normal(self, in_template: bool) -> None:
+        """One master regular expression recognises the frequent tokens; the
+        branches below it handle what needs state (strings, heredocs, the brace
+        that ends a template sequence) or is rare (non-ASCII identifiers)."""
         depth = 0
+        src, n = self.src, self.n
+        match = _NORMAL_RE.match
         while True:
-            self._skip_ws()
-            if self.pos >= self.n:
+            m = match(src, self.pos)
+            if m is not None:
+                kind = m.lastgroup
+                text = m.group(kind)
+                if kind == "ws":
+                    self._pending_ws += text
+                    self.pos = m.end()
+                    self.col += len(text)
+                    continue
+                if kind == "ident":
+                    end = m.end()
+                    if end < n and src[end] >= "\x80" and is_id_continue(src[end]):
+                        while end < n and is_id_continue(src[end]):
+                            end += 1
+                        text = src[self.pos:end]
+                    self._emit(T.IDENT, text)
+                elif kind == "nl":
+                    self._emit(T.NEWLINE, text)
+                elif kind == "comment":
+                    self._emit(T.COMMENT, text)
+                elif kind == "num":
+                    self._emit(T.NUMBER_LIT, text)
+                elif kind == "op2":
+                    self._emit(_TWO_CHAR[text], text)
+                elif kind == "dots":
+                    self._emit(T.ELLIPSIS, text)
+                else:   # op1: single-character operators other than braces
+                    self._emit(_ONE_CHAR[text], text)
+                continue
+            if self.pos >= n:
                 return
-            ch = self._peek()
-            nx = self._peek(1)
-
-            if ch == "\n":
-                self._emit(T.NEWLINE, "\n")
-            elif ch == "\r" and nx == "\n":
-                self._emit(T.NEWLINE, "\r\n")
-            elif ch == "#" or (ch == "/" and nx == "/"):
-                end = self.src.find("\n", self.pos)
-                end = self.n if end < 0 else end + 1
-                self._emit(T.COMMENT, self.src[self.pos:end])
-            elif ch == "/" and nx == "*":
-                end = self.src.find("*/", self.pos + 2)
-                if end < 0:
-                    self._emit(T.INVALID, self.src[self.pos:])
-                else:
-                    self._emit(T.COMMENT, self.src[self.pos:end + 2])
-            elif ch == '"':
+            ch = src[self.pos]
+            nx = src[self.pos + 1] if self.pos + 1 < n else ""
+            if ch == '"':
                 self._emit(T.OQUOTE, '"')
                 self._quoted()
             elif ch == "<" and nx == "<" and self._heredoc_intro():
                 pass
-            elif "0" <= ch <= "9":
-                self._number()
-            elif is_id_start(ch):
-                j = self.pos + 1
-                while j < self.n and is_id_continue(self.src[j]):
-                    j += 1
-                self._emit(T.IDENT, self.src[self.pos:j])
-            elif ch == "$" and nx == "{":
-                # only meaningful inside templates; invalid in normal mode
-                self._emit(T.INVALID, "${")
-            elif self.src.startswith("...", self.pos):
-                self._emit(T.ELLIPSIS, "...")
-            elif ch + nx in _TWO_CHAR:
-                self._emit(_TWO_CHAR[ch + nx], ch + nx)
+            elif ch == "{":
+                depth += 1
+                self._emit(T.OBRACE, "{")
             elif ch == "~" and nx == "}" and in_template and depth == 0:
                 self._emit(T.TEMPLATE_SEQ_END, "~}")
                 return
-            elif ch == "}" and in_template and depth == 0:
-                self._emit(T.TEMPLATE_SEQ_END, "}")
-                return
-            elif ch in _ONE_CHAR:
-                if ch == "{":
-                    depth += 1
-                elif ch == "}":
-                    depth -= 1
-                self._emit(_ONE_CHAR[ch], ch)
+            elif ch == "}":
+                if in_template and depth == 0:
+                    self._emit(T.TEMPLATE_SEQ_END, "}")
+                    return
+                depth -= 1
+                self._emit(T.CBRACE, "}")
+            elif ch == "/" and nx == "*":
+                self._emit(T.INVALID, src[self.pos:])       # unterminated block comment
+            elif ch == "<":
+                self._emit(T.LESS_THAN, "<")
+            elif is_id_start(ch):
+                j = self.pos + 1
+                while j < n and is_id_continue(src[j]):
+                    j += 1
+                self._emit(T.IDENT, src[self.pos:j])
+            elif ch == "$" and nx == "{":
+                # only meaningful inside templates; invalid in normal mode
+                self._emit(T.INVALID, "${")
             else:
                 self._emit(T.INVALID, ch)
-
-    def _number(self) -> None:
-        j = self.pos
-        while j < self.n and self.src[j].isdigit() and self.src[j] < "\x80":
-            j += 1
-        if j + 1 < self.n and self.src[j] == "." and "0" <= self.src[j + 1] <= "9":
-            j += 1
-            while j < self.n and "0" <= self.src[j] <= "9":
-                j += 1
-        if j < self.n and self.src[j] in "eE":
-            k = j + 1
-            if k < self.n and self.src[k] in "+-":
-                k += 1
-            if k < self.n and "0" <= self.src[k] <= "9":
-                while k < self.n and "0" <= self.src[k] <= "9":
-                    k += 1
-                j = k
-        self._emit(T.NUMBER_LIT, self.src[self.pos:j])
 
     # -- quoted template mode ----------------------------------------------
     def _lit(self, typ: T, end: int) -> None:

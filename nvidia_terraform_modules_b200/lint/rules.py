@@ -67,10 +67,13 @@ def _d(r_id: str, sev: str, summary: str, detail: str, file: str, node) -> Diagn
     return Diagnostic(sev, summary, detail, file, int(node), 0, r_id)
 
 
-def _all_exprs(m: Module) -> Iterator[tuple[str, A.Node]]:
-    for f in m.files:
-        for node in f.body.walk():
-            yield f.path, node
+def _all_exprs(m: Module) -> list[tuple[str, A.Node]]:
+    """Every syntax node of the module with its file, flattened once and kept
+    on the (read-only) module so that each rule does not walk the trees again."""
+    nodes = getattr(m, "_flat_nodes", None)
+    if nodes is None:
+        nodes = m._flat_nodes = [(f.path, node) for f in m.files for node in f.body.walk()]
+    return nodes
 
 
 def _expr_text(m: Module, file: str, attr: A.Attribute) -> str:
