@@ -298,6 +298,44 @@ class _Loader:
     def block_other(self, f: SourceFile, b: A.Block) -> None:
         pass
 
+    def require(self, f: SourceFile, b: A.Block, *names: str) -> None:
+        attrs = b.body.attributes
+        for n in names:
+            if n not in attrs:
+                self.diag(ERROR, "Missing required argument",
+                          f"The argument \"{n}\" is required, but no definition was found.", f.path, b, "structure")
+
+    def condition_block(self, f: SourceFile, b: A.Block) -> None:
+        """precondition / postcondition / validation / assert"""
+        self.check_args(f, b, {"condition", "error_message"}, {})
+        self.require(f, b, "condition", "error_message")
+
+    def block_moved(self, f: SourceFile, b: A.Block) -> None:
+        self.check_args(f, b, {"from", "to"}, {})
+        self.require(f, b, "from", "to")
+
+    def block_import(self, f: SourceFile, b: A.Block) -> None:
+        self.check_args(f, b, {"to", "id", "provider", "for_each"}, {})
+        self.require(f, b, "to", "id")
+
+    def block_removed(self, f: SourceFile, b: A.Block) -> None:
+        self.check_args(f, b, {"from"}, {"lifecycle": 0, "provisioner": 1})
+        self.require(f, b, "from")
+
+    def block_check(self, f: SourceFile, b: A.Block) -> None:
+        if not self.check_name(f, b, b.labels[0].value, "check block name"):
+            return
+        self.check_args(f, b, set(), {"assert": 0, "data": 2})
+        asserts = b.body.blocks_of("assert")
+        if not asserts:
+            self.diag(ERROR, "Invalid check block", "Check blocks must have at least one assert block.",
+                      f.path, b, "structure")
+        for a in asserts:
+            self.condition_block(f, a)
+        if len(b.body.blocks_of("data")) > 1:
+            self.diag(ERROR, "Multiple nested data resources",
+                      "Check blocks can only contain one nested data resource.", f.path, b, "structure")
+
     def block_variable(self, f: SourceFile, b: A.Block) -> None:
         name = b.labels[0].value
         if not self.check_name(f, b, name, "variable name"):
@@ -307,6 +345,16 @@ class _Loader:
                       f"The variable name \"{name}\" is reserved due to its special meaning inside module blocks.",
                       f.path, b, "structure")
         self.check_args(f, b, VARIABLE_ARGS, {"validation": 0})
+        for vb in b.body.blocks_of("validation"):
+            self.condition_block(f, vb)
+            cond = vb.body.attributes.get("condition")
+            if cond is not None:
+                refs = [n for n in cond.expr.walk() if isinstance(n, A.ScopeTraversal)]
+                own = any(r.root == "var" and r.steps and r.steps[0].value == name for r in refs)
+                if not own:
+                    self.diag(ERROR, "Invalid variable validation condition",
+                              f"The condition for variable \"{name}\" must refer to var.{name} in order to test "
+                              "incoming values.", f.path, cond.expr, "structure")
         if self.duplicate(f, b, self.m.variables, name, "Duplicate variable declaration",
                           f"A variable named \"{name}\" was already declared at {{prev}}. "
                           "Variable names must be unique within a module."):
@@ -360,6 +408,8 @@ class _Loader:
         if not self.check_name(f, b, name, "output name"):
             return
         self.check_args(f, b, OUTPUT_ARGS, {"precondition": 0})
+        for pb in b.body.blocks_of("precondition"):
+            self.condition_block(f, pb)
         attrs = b.body.attributes
         if "value" not in attrs:
             self.diag(ERROR, "Missing required argument",
@@ -466,6 +516,15 @@ class _Loader:
                 seen_lifecycle = True
                 self.check_args(f, blk, LIFECYCLE_ARGS if mode == "managed" else set(),
                                 {"precondition": 0, "postcondition": 0})
+                for cb in blk.body.blocks:
+                    if cb.type in ("precondition", "postcondition"):
+                        self.condition_block(f, cb)
+                ic = blk.body.attributes.get("ignore_changes")
+                if ic is not None and not isinstance(ic.expr, A.TupleCons) and not (
+                        isinstance(ic.expr, A.ScopeTraversal) and ic.expr.root == "all" and not ic.expr.steps):
+                    self.diag(ERROR, "Invalid ignore_changes ruleset",
+                              "The ignore_changes argument must be either a list of attribute names or the "
+                              "special keyword \"all\".", f.path, ic.expr, "structure")
             elif blk.type in ("provisioner", "connection") and mode == "data":
                 self.diag(ERROR, "Unsupported block type" if blk.type == "connection"
                           else "Data resources do not have provisioners",
@@ -562,6 +621,19 @@ class _Loader:
                     self.m.required_versions.append(
                         (text, Decl("required_version", f.path, attrs["required_version"].pos.line,
                                     attr=attrs["required_version"])))
+        backends = b.body.blocks_of("backend")
+        if len(backends) > 1:
+            self.diag(ERROR, "Duplicate backend configuration",
+                      f"A module may have only one backend configuration. The backend was previously configured at "
+                      f"{f.path}:{backends[0].pos.line}.", f.path, backends[1], "duplicate")
+        for be in backends:
+            for node in be.body.walk():
+                if isinstance(node, A.ScopeTraversal):
+                    self.diag(ERROR, "Variables not allowed", "Variables may not be used here.",
+                              f.path, node, "structure")
+                elif isinstance(node, A.FunctionCall):
+                    self.diag(ERROR, "Function calls not allowed", "Functions may not be called here.",
+                              f.path, node, "structure")
         rp_blocks = b.body.blocks_of("required_providers")
         for rp in rp_blocks:
             self.required_providers(f, rp)

@@ -68,6 +68,8 @@ class Validator:
     used_locals: set = field(default_factory=set)
     used_resources: set = field(default_factory=set)
     used_modules: set = field(default_factory=set)
+    edges: dict = field(default_factory=dict)       # who refers to whom, for cycle detection
+    _owner: Optional[str] = None
 
     # -- plumbing ------------------------------------------------------------
     def diag(self, sev: str, summary: str, detail: str, ctx: Ctx, node, rule: str) -> None:
@@ -97,7 +99,49 @@ class Validator:
                     handler = getattr(self, "visit_" + item.type, None)
                     if handler:
                         handler(f, item)
+        self.cycles()
         return self.diags
+
+    def cycles(self) -> None:
+        """Dependency cycles among local values, resources and data sources
+        (module calls are left out: Terraform orders them per input/output, and
+        a registry module's internals are not visible offline)."""
+        WHITE, GREY, BLACK = 0, 1, 2
+        colour: dict[str, int] = {}
+        reported: set[frozenset] = set()
+
+        def where(addr: str) -> tuple[str, int]:
+            if addr.startswith("local."):
+                d = self.m.locals[addr[6:]]
+            else:
+                d = self.m.resources[addr]
+            return d.file, d.line
+
+        def visit(node: str, path: list[str]) -> None:
+            colour[node] = GREY
+            path.append(node)
+            for nxt in sorted(self.edges.get(node, ())):
+                if nxt == node:
+                    continue                      # reported as self-reference
+                c = colour.get(nxt, WHITE)
+                if c == GREY:
+                    cyc = path[path.index(nxt):]
+                    key = frozenset(cyc)
+                    if key not in reported:
+                        reported.add(key)
+                        file, line = where(cyc[0])
+                        self.diags.append(Diagnostic(ERROR, "Cycle: " + ", ".join(sorted(cyc)),
+                                                     "These objects refer to each other in a circle, so no order "
+                                                     "exists in which Terraform could evaluate them.",
+                                                     file, line, 0, "cycle"))
+                elif c == WHITE:
+                    visit(nxt, path)
+            path.pop()
+            colour[node] = BLACK
+
+        for node in sorted(self.edges):
+            if colour.get(node, WHITE) == WHITE:
+                visit(node, [])
 
     # -- blocks --------------------------------------------------------------
     def visit_variable(self, f: SourceFile, b: A.Block) -> None:
@@ -114,7 +158,11 @@ class Validator:
         ctx = Ctx(f.path, where="locals")
         for item in b.body.items:
             if isinstance(item, A.Attribute):
-                self.attr_value(item, ctx)
+                self._owner = f"local.{item.name}"
+                try:
+                    self.attr_value(item, ctx)
+                finally:
+                    self._owner = None
 
     def visit_output(self, f: SourceFile, b: A.Block) -> None:
         ctx = Ctx(f.path, where="output")
@@ -146,6 +194,15 @@ class Validator:
             self.diag(ERROR, "Unreadable module directory",
                       f"Unable to evaluate directory symlink or the directory \"{mc.source}\" does not exist.",
                       base, b, "module-source")
+        if child is not None and child.providers:
+            hard = [a for a in ("count", "for_each", "depends_on") if a in b.body.attributes]
+            if hard:
+                p = child.providers[0]
+                self.diag(ERROR, "Module is incompatible with count, for_each, and depends_on",
+                          f"The module at module.{mc.name} is a legacy module which contains its own local provider "
+                          f"configurations, and so calls to it may not use the {', '.join(hard)} argument"
+                          f"{'s' if len(hard) > 1 else ''}. (provider \"{p.name}\" is configured at "
+                          f"{p.file}:{p.line}.)", base, b.body.attributes[hard[0]], "legacy-module")
         passed: set[str] = set()
         for name, attr in b.body.attributes.items():
             if name in ("source", "version"):
@@ -185,6 +242,13 @@ class Validator:
             return
         base = Ctx(f.path, where="resource" if mode == "managed" else "data")
         ctx = base.but(count=r.has_count, each=r.has_for_each)
+        self._owner = addr
+        try:
+            self._resource_body(b, r, base, ctx)
+        finally:
+            self._owner = None
+
+    def _resource_body(self, b: A.Block, r: Resource, base: Ctx, ctx: Ctx) -> None:
         for name, attr in b.body.attributes.items():
             if name in ("count", "for_each"):
                 self.attr_value(attr, base)
@@ -384,6 +448,12 @@ class Validator:
                           ctx, t, "undeclared-local")
             else:
                 self.used_locals.add(name)
+                if self._owner == f"local.{name}":
+                    self.diag(ERROR, "Self-referencing local value",
+                              f"Local value \"{name}\" cannot use its own result as part of its expression.",
+                              ctx, t, "self-reference")
+                elif self._owner:
+                    self.edges.setdefault(self._owner, set()).add(f"local.{name}")
         elif root == "module":
             self.module_ref(t, ctx, keyed)
         elif root == "data":
@@ -455,6 +525,11 @@ class Validator:
                       ctx, t, "undeclared-resource")
             return
         self.used_resources.add(addr)
+        if self._owner and self._owner != addr:
+            self.edges.setdefault(self._owner, set()).add(addr)
+        if self._owner == addr and not ctx.self_ok:
+            self.diag(ERROR, "Self-referential block",
+                      f"Configuration for {addr} may not refer to itself.", ctx, t, "self-reference")
         multi = r.has_count or r.has_for_each
         has_key = bool(rest) and rest[0].kind == "index"
         if not rest and keyed:

@@ -486,6 +486,43 @@ def counterpart_mismatch(c: LintContext):
                         yield note(file, k, "object key", ref, own, other)
 
 
+@rule("duplicate-object-key", WARNING, "object constructor sets the same key twice", "terraform_map_duplicate_keys")
+def duplicate_object_key(c: LintContext):
+    for file, node in _all_exprs(c.m):
+        if isinstance(node, A.ObjectCons):
+            seen: dict[str, A.Node] = {}
+            for key, _ in node.items:
+                k = key.literal_key()
+                if k is None:
+                    continue
+                if k in seen:
+                    yield _d("duplicate-object-key", WARNING, f"key \"{k}\" is set twice in one object",
+                             f"The later value silently replaces the one at line {seen[k].pos.line}.", file, key)
+                else:
+                    seen[k] = key
+
+
+@rule("empty-list-equality", WARNING, "comparison with [] is always false", "terraform_empty_list_equality")
+def empty_list_equality(c: LintContext):
+    for file, node in _all_exprs(c.m):
+        if isinstance(node, A.Binary) and node.op in ("==", "!="):
+            for side in (node.lhs, node.rhs):
+                if isinstance(side, A.TupleCons) and not side.items:
+                    yield _d("empty-list-equality", WARNING, "Comparing a collection with an empty list",
+                             "[] is an empty tuple, which never equals a list(...) value, so this is always "
+                             f"{'false' if node.op == '==' else 'true'}; use length(x) == 0 instead.", file, node)
+                    break
+
+
+@rule("deprecated-lookup", NOTICE, "lookup() with two arguments", "terraform_deprecated_lookup")
+def deprecated_lookup(c: LintContext):
+    for file, node in _all_exprs(c.m):
+        if isinstance(node, A.FunctionCall) and node.name == "lookup" and len(node.args) == 2 \
+                and not node.expand_final:
+            yield _d("deprecated-lookup", NOTICE, "lookup() without a default",
+                     "With two arguments lookup(m, k) is just m[k]; the index syntax is preferred.", file, node)
+
+
 @rule("provider-in-module", NOTICE, "provider configuration inside a module that other modules call")
 def provider_in_module(c: LintContext):
     # A module with its own provider blocks cannot be used with count, for_each
@@ -496,12 +533,11 @@ def provider_in_module(c: LintContext):
         mc = c.m.module_calls[name]
         p = child.providers[0]
         attrs = mc.block.body.attributes if mc.block else {}
-        hard = [a for a in ("count", "for_each", "depends_on") if a in attrs]
-        sev = WARNING if hard else NOTICE
-        yield _d("provider-in-module", sev,
+        if any(a in attrs for a in ("count", "for_each", "depends_on")):
+            continue            # validate already reports that combination as an error
+        yield _d("provider-in-module", NOTICE,
                  f"module \"{name}\" ({mc.source}) contains its own provider \"{p.name}\" configuration",
-                 ("This call uses " + ", ".join(hard) + ", which Terraform rejects for such modules. " if hard else "")
-                 + "A module with provider blocks is a legacy module: callers cannot use count, for_each or "
+                 "A module with provider blocks is a legacy module: callers cannot use count, for_each or "
                  "depends_on with it, and removing the call later orphans its resources' provider "
                  f"(declared at {p.file}:{p.line}).", mc.file, mc.line)
 

@@ -77,6 +77,10 @@ def test_tidy_module_has_no_findings(module_dir):
      'resource "x_pool" "gpu_nodes" {\n  tags = var.gpu_tags\n}\nresource "x_pool" "both_cpu_gpu" {\n'
      '  tags = var.gpu_tags\n}\nlocals {\n  pools = {\n    cpu_pool = { t = var.cpu_tags }\n'
      '    private-a = { t = var.public_x }\n  }\n}\nvariable "public_x" {}\n', [4, 15]),
+    ("duplicate-object-key", 'locals {\n  a = {\n    k = 1\n    "k" = 2\n    j = 3\n  }\n}\n', [4]),
+    ("empty-list-equality", 'variable "l" {}\nlocals {\n  a = var.l == []\n  b = length(var.l) == 0\n'
+                            '  c = [] != var.l\n}\n', [3, 5]),
+    ("deprecated-lookup", 'variable "m" {}\nlocals {\n  a = lookup(var.m, "k")\n  b = lookup(var.m, "k", 1)\n}\n', [3]),
     ("local-exec", 'resource "null_resource" "n" {\n  provisioner "local-exec" {\n    command = "helm repo add x y"\n'
                    '  }\n}\n', [2]),
 ])
@@ -107,7 +111,8 @@ def test_provider_in_called_module(module_dir):
     }
     res = validate_module(module_dir(files))
     found = [(d.severity, d.line) for d in run_rules(res, only={"provider-in-module"})]
-    assert found == [("notice", 1), ("warning", 4)]
+    assert found == [("notice", 1)]          # the counted call is validate's error, not repeated here
+    assert [d.summary for d in res.diags] == ["Module is incompatible with count, for_each, and depends_on"]
 
 
 def test_unused_provider_passed_to_child_is_used(module_dir):

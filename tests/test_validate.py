@@ -283,6 +283,53 @@ def test_version_is_only_for_registry_sources(module_dir):
     assert [s for _, s in diags] == ["Invalid registry module source address"]
 
 
+def test_self_references_and_cycles(module_dir):
+    text = '''
+locals {
+  a = local.b
+  b = local.c
+  c = [local.a]
+  me = local.me
+  fine = local.a
+}
+resource "aws_a" "x" {
+  name = aws_a.x.id
+  peer = aws_a.y.id
+  provisioner "local-exec" {
+    command = "echo ${aws_a.x.id} ${self.id}"
+  }
+}
+resource "aws_a" "y" {
+  peer = data.aws_d.z.id
+}
+data "aws_d" "z" {
+  v = aws_a.x.id
+}
+'''
+    assert summaries(module_dir, text) == ["Cycle: local.a, local.b, local.c", "Self-referencing local value",
+                                           "Cycle: aws_a.x, aws_a.y, data.aws_d.z", "Self-referential block"]
+
+
+@pytest.mark.parametrize("text,summary", [
+    ('variable "a" {\n  validation {\n    condition     = true\n    error_message = "m"\n  }\n}\n',
+     "Invalid variable validation condition"),
+    ('variable "a" {\n  validation {\n    condition = var.a != ""\n  }\n}\n', "Missing required argument"),
+    ('output "o" {\n  value = 1\n  precondition {\n    error_message = "m"\n  }\n}\n', "Missing required argument"),
+    ('resource "a_b" "c" {\n  lifecycle {\n    ignore_changes = "tags"\n  }\n}\n', "Invalid ignore_changes ruleset"),
+    ('resource "a_b" "c" {\n  lifecycle {\n    ignore_changes = all\n  }\n}\n', None),
+    ('resource "a_b" "c" {\n  lifecycle {\n    postcondition {\n      condition = self.id != ""\n'
+     '      error_message = "m"\n    }\n  }\n}\n', None),
+    ('variable "b" {}\nterraform {\n  backend "s3" {\n    bucket = var.b\n  }\n}\n', "Variables not allowed"),
+    ('terraform {\n  backend "s3" {}\n  backend "gcs" {}\n}\n', "Duplicate backend configuration"),
+    ('moved {\n  from = aws_a.b\n}\n', "Missing required argument"),
+    ('import {\n  to = aws_a.b\n  id = "x"\n}\nresource "aws_a" "b" {}\n', None),
+    ('check "health" {\n}\n', "Invalid check block"),
+    ('check "health" {\n  assert {\n    condition     = 1 == 1\n    error_message = "m"\n  }\n}\n', None),
+])
+def test_more_structural_rules(module_dir, text, summary):
+    assert summaries(module_dir, text) == ([summary] if summary else [])
+
+
 def test_aliased_providers_are_distinct(module_dir):
     assert summaries(module_dir, 'provider "aws" {}\nprovider "aws" {\n  alias = "west"\n}\n'
                                  'resource "aws_a" "b" {\n  provider = aws.west\n}\n') == []
