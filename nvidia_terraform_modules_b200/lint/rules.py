@@ -558,6 +558,40 @@ def local_exec(c: LintContext):
                          "to \"terraform plan\", and it is not undone by \"terraform destroy\".", r.file, blk)
 
 
+@rule("helper-script", WARNING, "shell helper beside the module is unreferenced, has an inert shebang or evals input")
+def helper_script(c: LintContext):
+    """Shell scripts shipped next to ``.tf`` files are meant for ``external`` data
+    sources or ``local-exec`` (the reference ships eks/setup-kube-config.sh)."""
+    try:
+        scripts = sorted(n for n in os.listdir(c.m.dir) if n.endswith((".sh", ".bash")))
+    except OSError:
+        return
+    if not scripts:
+        return
+    base = os.path.dirname(c.m.files[0].path) if c.m.files else c.m.dir
+    hcl_text = "\n".join(f.src for f in c.m.files)
+    for name in scripts:
+        with open(os.path.join(c.m.dir, name), "r", encoding="utf-8", errors="replace") as fh:
+            lines = fh.read().split("\n")
+        disp = os.path.join(base, name)
+        if name not in hcl_text:
+            yield Diagnostic(WARNING, f"{name} is not referenced by any .tf file of this module",
+                             "No external data source, provisioner, file() or templatefile() call names it; it is "
+                             "dead code or undocumented manual tooling.", disp, 1, 0, "helper-script")
+        shebang = next((i for i, ln in enumerate(lines) if ln.startswith("#!")), None)
+        if shebang is not None and shebang > 0:
+            yield Diagnostic(WARNING, f"{name}: the #! line is on line {shebang + 1}, not line 1",
+                             "The kernel only honours an interpreter line that is the very first line; here the "
+                             "script runs under whatever shell the caller happens to use.", disp, shebang + 1, 0,
+                             "helper-script")
+        for i, ln in enumerate(lines):
+            if re.search(r"(^|[;&|]\s*)eval\s", ln.strip()):
+                yield Diagnostic(WARNING, f"{name}: eval of generated text",
+                                 "eval executes whatever the expansion produces; with input that arrives on stdin "
+                                 "(the external data source protocol) that is command injection unless every value "
+                                 "is shell-quoted.", disp, i + 1, 0, "helper-script")
+
+
 # ---------------------------------------------------------------------------
 def run_rules(result: ValidateResult, only: Optional[set[str]] = None,
               skip: Optional[set[str]] = None) -> list[Diagnostic]:

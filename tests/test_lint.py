@@ -126,3 +126,14 @@ def test_only_and_skip(module_dir):
     assert {"comment-syntax", "unused-variable"} <= everything
     assert {d.rule for d in run_rules(res, only={"comment-syntax"})} == {"comment-syntax"}
     assert "comment-syntax" not in {d.rule for d in run_rules(res, skip={"comment-syntax"})}
+
+
+def test_helper_script_rule(module_dir):
+    files = {
+        "main.tf": 'data "external" "x" {\n  program = ["bash", "${path.module}/used.sh"]\n}\n',
+        "used.sh": "#!/bin/bash\necho '{}'\n",
+        "stale.sh": "# licence header\n\n#!/bin/bash\nset -e\neval \"$(jq -r '@sh \"A=\\(.a)\"')\"\n",
+    }
+    res = validate_module(module_dir(files))
+    got = [(d.file.rsplit("/", 1)[-1], d.line) for d in run_rules(res, only={"helper-script"})]
+    assert got == [("stale.sh", 1), ("stale.sh", 3), ("stale.sh", 5)]

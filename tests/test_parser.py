@@ -163,6 +163,13 @@ def test_unescape():
     assert unescape_quoted('a\\n\\t\\"\\\\ $${x} %%{y} \\u00e9') == 'a\n\t"\\ ${x} %{y} é'
 
 
+def test_dash_belongs_to_the_identifier_before_it():
+    # HCL names may contain dashes, so "a-1" is a single name and "a - 1" a subtraction
+    assert expr("var.a-1").steps[0].value == "a-1"
+    assert isinstance(expr("var.a - 1"), A.Binary)
+    assert errors('x = true-"s"\n') == [("Missing newline after argument", 1, 10)]
+
+
 def test_parentheses_allow_newlines():
     e = expr("(\n  a\n  + b\n)")
     assert isinstance(e, A.Parens) and e.inner.op == "+"

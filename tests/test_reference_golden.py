@@ -47,6 +47,9 @@ ACCEPTANCE = [
     ("eks", "required-provider-missing", "eks/main.tf", 185),   # helm used, not declared
     ("eks", "required-provider-unused", "eks/versions.tf", 10),  # kubernetes declared, unused
     ("eks", "legacy-splat", "eks/output.tf", 5),
+    ("eks", "helper-script", "eks/setup-kube-config.sh", 1),    # orphaned (CHANGELOG.md:11)
+    ("eks", "helper-script", "eks/setup-kube-config.sh", 4),    # shebang after the licence comments
+    ("eks", "helper-script", "eks/setup-kube-config.sh", 6),    # eval of jq output
     ("aks", "unused-variable", "aks/variables.tf", 54),         # cpu_os_sku
     ("aks", "unused-variable", "aks/variables.tf", 82),         # gpu_os_sku
     ("aks", "required-provider-unused", "aks/versions.tf", 10),
