@@ -36,8 +36,6 @@ RESERVED_VARIABLE_NAMES = {"source", "version", "providers", "count", "for_each"
 VARIABLE_ARGS = {"description", "default", "type", "sensitive", "nullable", "ephemeral"}
 OUTPUT_ARGS = {"description", "value", "sensitive", "depends_on", "ephemeral"}
 LIFECYCLE_ARGS = {"create_before_destroy", "prevent_destroy", "ignore_changes", "replace_triggered_by"}
-RESOURCE_META_ARGS = {"count", "for_each", "provider", "depends_on"}
-MODULE_META_ARGS = {"source", "version", "count", "for_each", "depends_on", "providers"}
 
 
 @dataclass

@@ -22,7 +22,7 @@ from typing import Optional
 
 from ..config import typeexpr
 from ..config.lockfile import LockFile
-from ..config.model import Module, SourceFile, Variable
+from ..config.model import Module, Variable
 from ..hcl import ast as A
 from ..hcl.diagnostics import Diagnostic, WARNING
 from ..hcl.tokens import T

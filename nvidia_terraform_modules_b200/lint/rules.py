@@ -21,7 +21,7 @@ from ..config.model import Module, Resource
 from ..config.validate import ValidateResult, Validator
 from ..hcl import ast as A
 from ..hcl.diagnostics import Diagnostic, NOTICE, WARNING
-from ..hcl.tokens import T, render
+from ..hcl.tokens import T
 
 _SNAKE = re.compile(r"^[a-z][a-z0-9_]*$")
 _SECRETISH = re.compile(r"(secret|password|passwd|token|private_key|shared_key|access_key|client_certificate)",
