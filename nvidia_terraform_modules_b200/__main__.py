@@ -8,12 +8,14 @@ Sub-commands mirror the tools the reference's contribution guide names
     lint      [--only RULES] [--skip RULES] [--json] [DIR...]
     lock      [DIR...]            lock file vs. required_providers
     docs      [--check] [DIR]     terraform-docs style tables / README drift
-    check     [--json] [ROOT]     everything, every module under ROOT
+    check     [--json] [--strict] [ROOT]   everything, every module under ROOT
     report    [-o FILE] [ROOT]    markdown issue list of `check`
 
 Exit codes: fmt as ``terraform fmt`` (0, 2 syntax error, 3 -check found diffs);
 validate 1 when invalid; lint/lock/docs/check 1 when anything of severity
-warning or above (check: error or unformatted file) was found.
+warning or above (check: error or unformatted file; with --strict also warnings)
+was found.  A comment ``# tfcheck-ignore: rule-a, rule-b`` (or ``all``) silences lint
+rules on its own line and the next one.
 """
 from __future__ import annotations
 
@@ -127,6 +129,7 @@ def cmd_docs(argv: list[str]) -> int:
 
 def cmd_check(argv: list[str]) -> int:
     as_json = any(a in ("-json", "--json") for a in argv)
+    strict = "--strict" in argv
     roots = [a for a in argv if not a.startswith("-")] or ["."]
     rep = check_tree(os.path.abspath(roots[0]))
     if as_json:
@@ -141,6 +144,8 @@ def cmd_check(argv: list[str]) -> int:
               f"{rep.seconds * 1000:.0f} ms: {c['fmt_differing']} unformatted, {c['error']} errors, "
               f"{c['warning']} warnings, {c['notice']} notices")
         print(f"(note: {STAND_IN})")
+    if strict and rep.count(WARNING):
+        return 1
     return 0 if rep.ok else 1
 
 

@@ -606,5 +606,30 @@ def run_rules(result: ValidateResult, only: Optional[set[str]] = None,
         if skip and r.id in skip:
             continue
         out.extend(r.fn(ctx))
+    ignored = _ignore_comments(result.module)
+    out = [d for d in out if not _is_ignored(d, ignored)]
     out.sort(key=lambda d: (d.file, d.line, d.col, d.rule))
     return out
+
+
+_IGNORE_RE = re.compile(r"^(?:#|//)\s*tfcheck-ignore:\s*([A-Za-z0-9_,\- ]+)")
+
+
+def _ignore_comments(m: Module) -> dict[tuple[str, int], set[str]]:
+    """``# tfcheck-ignore: rule-a, rule-b`` silences those rules (or ``all``) on
+    its own line and on the line that follows it."""
+    table: dict[tuple[str, int], set[str]] = {}
+    for f in m.files:
+        for t in f.tokens:
+            if t.type is T.COMMENT:
+                hit = _IGNORE_RE.match(t.text)
+                if hit:
+                    rules = {r.strip() for r in hit.group(1).split(",") if r.strip()}
+                    for line in (t.line, t.line + 1):
+                        table.setdefault((f.path, line), set()).update(rules)
+    return table
+
+
+def _is_ignored(d: Diagnostic, table: dict[tuple[str, int], set[str]]) -> bool:
+    rules = table.get((d.file, d.line))
+    return bool(rules) and (d.rule in rules or "all" in rules)

@@ -70,6 +70,7 @@ def test_check_and_report(trees, tmp_path):
                                                                "unavailable"]
     p = cli(["check", "."], trees / "bad")
     assert p.returncode == 1 and "3 unformatted, 2 errors" in p.stdout
+    assert cli(["check", "--strict", "."], trees / "clean").returncode == 0
     out = tmp_path / "r.md"
     assert cli(["report", "-o", str(out), "."], trees / "bad").returncode == 0
     text = out.read_text()

@@ -137,3 +137,13 @@ def test_helper_script_rule(module_dir):
     res = validate_module(module_dir(files))
     got = [(d.file.rsplit("/", 1)[-1], d.line) for d in run_rules(res, only={"helper-script"})]
     assert got == [("stale.sh", 1), ("stale.sh", 3), ("stale.sh", 5)]
+
+
+def test_ignore_comments(module_dir):
+    text = ('# tfcheck-ignore: unused-variable\nvariable "a" {}\n'
+            'variable "b" {} # tfcheck-ignore: all\n'
+            '# tfcheck-ignore: untyped-variable\nvariable "c" {}\n'
+            '# an ordinary comment\nvariable "d" {}\n')
+    res = validate_module(module_dir({"main.tf": text}))
+    got = [(d.rule, d.line) for d in run_rules(res, only={"unused-variable", "untyped-variable"})]
+    assert got == [("untyped-variable", 2), ("unused-variable", 5), ("untyped-variable", 7), ("unused-variable", 7)]
