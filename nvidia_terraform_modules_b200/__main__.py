@@ -7,7 +7,7 @@ Sub-commands mirror the tools the reference's contribution guide names
     validate  [-json] [DIR]
     lint      [--only RULES] [--skip RULES] [--json] [DIR...]
     lock      [DIR...]            lock file vs. required_providers
-    docs      [--check] [DIR]     terraform-docs style tables / README drift
+    docs      [--check|--write] [DIR]   terraform-docs style tables / README drift / update README in place
     check     [--json] [--strict] [ROOT]   everything, every module under ROOT
     report    [-o FILE] [ROOT]    markdown issue list of `check`
 
@@ -26,7 +26,7 @@ import sys
 from .check import STAND_IN, check_tree
 from .config.lockfile import check_lock_consistency, load_lockfile
 from .config.validate import validate_module
-from .docs.tfdocs import check_readme, find_readme, render
+from .docs.tfdocs import check_readme, find_readme, inject, render
 from .fmt import command as fmt_command
 from .hcl.diagnostics import ERROR, WARNING
 from .lint.rules import RULES, run_rules
@@ -114,6 +114,15 @@ def cmd_docs(argv: list[str]) -> int:
     check = "--check" in argv
     dirs = [a for a in argv if not a.startswith("-")] or ["."]
     res = validate_module(dirs[0], ".")
+    if "--write" in argv:
+        readme = find_readme(dirs[0]) or os.path.join(dirs[0], "README.md")
+        old = open(readme, encoding="utf-8").read() if os.path.isfile(readme) else ""
+        new = inject(old, render(res.module, load_lockfile(dirs[0], ".")))
+        if new != old:
+            with open(readme, "w", encoding="utf-8") as fh:
+                fh.write(new)
+            print(f"{readme} updated")
+        return 0
     if not check:
         sys.stdout.write(render(res.module, load_lockfile(dirs[0], ".")))
         return 0

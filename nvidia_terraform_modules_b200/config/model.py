@@ -426,6 +426,32 @@ class _Loader:
     def _count_for_each(self, f: SourceFile, b: A.Block) -> tuple[bool, bool]:
         attrs = b.body.attributes
         has_count, has_each = "count" in attrs, "for_each" in attrs
+        if has_count:
+            v = typeexpr.literal_value(attrs["count"].expr)
+            ok = v is typeexpr.UNKNOWN or (isinstance(v, (int, float)) and not isinstance(v, bool)) \
+                or (isinstance(v, str) and v.isdigit())
+            if v is None:
+                self.diag(ERROR, "Invalid count argument",
+                          "The given \"count\" argument value is null. An integer is required.",
+                          f.path, attrs["count"].expr, "type")
+            elif not ok:
+                self.diag(ERROR, "Incorrect value type", "Invalid expression value: number required.",
+                          f.path, attrs["count"].expr, "type")
+            elif isinstance(v, (int, float)) and (v < 0 or v != int(v)):
+                self.diag(ERROR, "Invalid count argument",
+                          "The given \"count\" argument value is unsuitable: must be a whole number that is "
+                          "greater than or equal to zero.", f.path, attrs["count"].expr, "type")
+        if has_each:
+            e = attrs["for_each"].expr
+            if isinstance(e, A.TupleCons) or (isinstance(e, A.ForExpr) and e.key_expr is None):
+                self.diag(ERROR, "Invalid for_each argument",
+                          "The given \"for_each\" argument value is unsuitable: the \"for_each\" argument must be "
+                          "a map, or set of strings, and you have provided a value of type tuple. Wrap it in "
+                          "toset(...) to use its elements as keys.", f.path, e, "type")
+            elif isinstance(e, A.Literal) or (isinstance(e, A.Template) and e.literal_value() is not None):
+                self.diag(ERROR, "Invalid for_each argument",
+                          "The given \"for_each\" argument value is unsuitable: the \"for_each\" argument must be "
+                          "a map, or set of strings.", f.path, e, "type")
         if has_count and has_each:
             self.diag(ERROR, "Invalid combination of \"count\" and \"for_each\"",
                       "The \"count\" and \"for_each\" meta-arguments are mutually-exclusive, only one should "

@@ -171,7 +171,7 @@ def render(m: Module, lock: Optional[LockFile] = None) -> str:
     out.append("\n## Resources\n")
     if m.resources:
         out.append("| Name | Type |\n|------|------|")
-        ordered = sorted(m.resources.values(), key=lambda r: (r.mode == "data", r.type, r.name))
+        ordered = sorted(m.resources.values(), key=lambda r: (r.mode == "data", doc_resource_name(r)))
         for r in ordered:
             req = m.required_providers.get(r.implied_provider)
             ns_type = req.source if req and req.source and req.source.count("/") == 1 \
@@ -446,6 +446,42 @@ def check_readme(m: Module, readme_path: str, display: Optional[str] = None) -> 
                 add(t.heading_line, f"requirement \"{name}\" is not documented in the README", "",
                     "docs-missing-requirement")
     return diags
+
+
+BEGIN_MARK = "<!-- BEGIN_TF_DOCS -->"
+END_MARK = "<!-- END_TF_DOCS -->"
+
+
+def inject(readme_text: str, tables: str) -> str:
+    """Put freshly rendered tables into a README, the three ways terraform-docs'
+    "inject" mode knows: between BEGIN/END markers when present; else in place of
+    the existing run of generated sections (from the first ``## Requirements``-style
+    heading to the end of the last generated table); else appended."""
+    tables = tables.rstrip("\n") + "\n"
+    if BEGIN_MARK in readme_text and END_MARK in readme_text:
+        head, rest = readme_text.split(BEGIN_MARK, 1)
+        _, tail = rest.split(END_MARK, 1)
+        return f"{head}{BEGIN_MARK}\n{tables}{END_MARK}{tail}"
+    lines = readme_text.split("\n")
+    starts = [i for i, ln in enumerate(lines)
+              if re.match(r"^##\s+(\w+)\s*$", ln) and re.match(r"^##\s+(\w+)\s*$", ln).group(1) in SECTIONS]
+    if not starts:
+        sep = "" if readme_text.endswith("\n\n") or not readme_text else ("\n" if readme_text.endswith("\n") else "\n\n")
+        return readme_text + sep + tables
+    first = starts[0]
+    # the generated run ends where the last generated section's table (or its
+    # one-line "No ..." sentence) ends
+    end = starts[-1] + 1
+    while end < len(lines) and not lines[end].startswith("#"):
+        end += 1
+    while end > starts[-1] + 1 and lines[end - 1].strip() == "":
+        end -= 1
+    tail = lines[end:]
+    out = lines[:first] + tables.rstrip("\n").split("\n") + tail
+    text = "\n".join(out)
+    if readme_text.endswith("\n") and not text.endswith("\n"):
+        text += "\n"
+    return text
 
 
 def find_readme(directory: str) -> Optional[str]:

@@ -523,6 +523,24 @@ def deprecated_lookup(c: LintContext):
                      "With two arguments lookup(m, k) is just m[k]; the index syntax is preferred.", file, node)
 
 
+@rule("sensitive-output", WARNING, "output exposes a sensitive variable without being marked sensitive")
+def sensitive_output(c: LintContext):
+    secret = {n for n, v in c.m.variables.items() if v.sensitive}
+    if not secret:
+        return
+    for name, o in c.m.outputs.items():
+        if o.sensitive or o.block is None or "value" not in o.block.body.attributes:
+            continue
+        for ref in o.block.body.attributes["value"].expr.walk():
+            if isinstance(ref, A.ScopeTraversal) and ref.root == "var" and ref.steps \
+                    and ref.steps[0].value in secret:
+                yield _d("sensitive-output", WARNING,
+                         f"output \"{name}\" is built from sensitive var.{ref.steps[0].value}",
+                         "Terraform stops the plan with \"Output refers to sensitive values\" unless the output "
+                         "sets sensitive = true.", o.file, ref)
+                break
+
+
 @rule("provider-in-module", NOTICE, "provider configuration inside a module that other modules call")
 def provider_in_module(c: LintContext):
     # A module with its own provider blocks cannot be used with count, for_each

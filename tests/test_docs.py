@@ -1,6 +1,6 @@
 """README tables: generation in terraform-docs' layout and drift detection."""
 from nvidia_terraform_modules_b200.config.model import load_module
-from nvidia_terraform_modules_b200.docs.tfdocs import check_readme, parse_readme, render
+from nvidia_terraform_modules_b200.docs.tfdocs import BEGIN_MARK, END_MARK, check_readme, inject, parse_readme, render
 
 FILES = {
     "versions.tf": 'terraform {\n  required_version = ">= 1.2.4"\n  required_providers {\n    aws = {\n'
@@ -113,3 +113,25 @@ def test_parse_readme_handles_escaped_pipes_and_line_numbers():
     t = parse_readme("x\n## Inputs\n\n| Name | Description |\n|---|---|\n| a | b \\| c |\n\n## Outputs\n\nNo outputs.\n")
     assert t["Inputs"].rows == [(6, ["a", "b | c"])]
     assert t["Outputs"].header == []
+
+
+def test_inject_replaces_stale_tables_and_keeps_the_prose(module_dir, tmp_path):
+    _, m = module(module_dir)
+    fresh = render(m)
+    stale = fresh.replace("| `true` | no |", "| `false` | no |").replace("| CA data |", "| old |")
+    before = "# Title\n\nintro\n\n" + stale + "\n## License\n\nApache\n"
+    after = inject(before, fresh)
+    assert after == "# Title\n\nintro\n\n" + fresh + "\n## License\n\nApache\n"
+    readme = tmp_path / "R.md"
+    readme.write_text(after)
+    assert check_readme(m, str(readme)) == []
+    assert inject(after, fresh) == after                      # idempotent
+
+
+def test_inject_between_markers_and_append(module_dir):
+    _, m = module(module_dir)
+    fresh = render(m)
+    marked = f"# T\n\n{BEGIN_MARK}\nold junk\n{END_MARK}\n\nfooter\n"
+    assert inject(marked, fresh) == f"# T\n\n{BEGIN_MARK}\n{fresh}{END_MARK}\n\nfooter\n"
+    assert inject("# T\n\nprose\n", fresh) == "# T\n\nprose\n\n" + fresh
+    assert inject("", fresh) == fresh

@@ -81,6 +81,10 @@ def test_tidy_module_has_no_findings(module_dir):
     ("empty-list-equality", 'variable "l" {}\nlocals {\n  a = var.l == []\n  b = length(var.l) == 0\n'
                             '  c = [] != var.l\n}\n', [3, 5]),
     ("deprecated-lookup", 'variable "m" {}\nlocals {\n  a = lookup(var.m, "k")\n  b = lookup(var.m, "k", 1)\n}\n', [3]),
+    ("sensitive-output", 'variable "pw" {\n  sensitive = true\n}\nvariable "n" {}\n'
+                         'output "a" {\n  value = "x-${var.pw}"\n}\n'
+                         'output "b" {\n  value     = var.pw\n  sensitive = true\n}\n'
+                         'output "c" {\n  value = var.n\n}\n', [6]),
     ("local-exec", 'resource "null_resource" "n" {\n  provisioner "local-exec" {\n    command = "helm repo add x y"\n'
                    '  }\n}\n', [2]),
 ])

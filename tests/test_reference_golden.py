@@ -162,3 +162,17 @@ def test_every_reference_hcl_file_round_trips_through_the_scanner(reference_root
                 assert render(toks, keep_raw=True) == src
                 seen += 1
     assert seen == 44       # 32 .tf + 6 .tfvars + 6 .hcl
+
+
+@pytest.mark.reference
+@pytest.mark.parametrize("module", ["eks", "gke", "aks", "aks/examples/cnpack"])
+def test_regenerating_an_up_to_date_readme_changes_nothing(reference_root, module):
+    """The whole generated region -- headings, table headers, row order, blank
+    lines -- equals what real terraform-docs wrote into these four READMEs."""
+    from nvidia_terraform_modules_b200.config.lockfile import load_lockfile
+    from nvidia_terraform_modules_b200.config.model import load_module
+    from nvidia_terraform_modules_b200.docs.tfdocs import find_readme, inject, render
+    d = os.path.join(reference_root, module)
+    with open(find_readme(d), encoding="utf-8") as fh:
+        text = fh.read()
+    assert inject(text, render(load_module(d, reference_root), load_lockfile(d, reference_root))) == text

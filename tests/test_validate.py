@@ -330,6 +330,19 @@ def test_more_structural_rules(module_dir, text, summary):
     assert summaries(module_dir, text) == ([summary] if summary else [])
 
 
+@pytest.mark.parametrize("arg,summary", [
+    ('count = "two"', "Incorrect value type"), ("count = null", "Invalid count argument"),
+    ("count = -1", "Invalid count argument"), ("count = 1.5", "Invalid count argument"),
+    ('count = "2"', None), ("count = 3", None), ("count = var.n", None),
+    ('for_each = ["a", "b"]', "Invalid for_each argument"), ("for_each = [for x in var.n : x]", "Invalid for_each argument"),
+    ('for_each = "a"', "Invalid for_each argument"), ('for_each = toset(["a"])', None),
+    ("for_each = { a = 1 }", None), ("for_each = { for x in var.n : x => x }", None),
+])
+def test_literal_count_and_for_each(module_dir, arg, summary):
+    text = f'variable "n" {{}}\nresource "a_b" "c" {{\n  {arg}\n}}\n'
+    assert summaries(module_dir, text) == ([summary] if summary else [])
+
+
 def test_aliased_providers_are_distinct(module_dir):
     assert summaries(module_dir, 'provider "aws" {}\nprovider "aws" {\n  alias = "west"\n}\n'
                                  'resource "aws_a" "b" {\n  provider = aws.west\n}\n') == []
