@@ -32,7 +32,7 @@ from typing import Optional
 from ..hcl import ast as A
 from ..hcl.diagnostics import Diagnostic, ERROR, WARNING, has_errors
 from ..hcl.parser import parse
-from . import functions, typeexpr
+from . import functions, kinds, typeexpr
 from .model import Module, ModuleCall, Resource, SourceFile, load_module
 
 _PATH_ATTRS = {"module", "root", "cwd"}
@@ -390,6 +390,19 @@ class Validator:
             if e.bare_name is None:
                 self.expr(e.wrapped, ctx)
         else:
+            if isinstance(e, A.Conditional):
+                clash = kinds.conditional_mismatch(e)
+                if clash:
+                    self.diag(ERROR, "Inconsistent conditional result types",
+                              "The true and false result expressions must have consistent types. The 'true' value "
+                              f"is {clash[0]}, but the 'false' value is {clash[1]}.", ctx, e, "type")
+            elif isinstance(e, (A.Binary, A.Unary)):
+                bad = kinds.operand_problem(e)
+                if bad:
+                    side, operand, need = bad
+                    self.diag(ERROR, "Invalid operand",
+                              f"Unsuitable value for {side + ' ' if side else ''}operand: {need} required.",
+                              ctx, operand, "type")
             for ch in e.children():
                 self.expr(ch, ctx)
 

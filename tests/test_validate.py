@@ -343,6 +343,24 @@ def test_literal_count_and_for_each(module_dir, arg, summary):
     assert summaries(module_dir, text) == ([summary] if summary else [])
 
 
+@pytest.mark.parametrize("expr,summary", [
+    ('var.n ? "a" : ["b"]', "Inconsistent conditional result types"),
+    ("var.n ? {} : []", "Inconsistent conditional result types"),
+    ("var.n ? 1 : false", "Inconsistent conditional result types"),
+    ("var.n ? length(var.n) : keys(var.n)", "Inconsistent conditional result types"),
+    ('var.n ? "a" : 1', None), ("var.n ? [] : var.n", None), ("var.n ? null : {}", None),
+    ("var.n ? { a = 1 } : {}", None), ("var.n ? [1] : tolist([])", None),
+    ('var.n ? "${var.n}" : []', "Interpolation-only expressions are deprecated"),   # passes var.n through: no type clash
+    ("[1] + 1", "Invalid operand"), ('"abc" * 2', "Invalid operand"), ('"12" * 2', None),
+    ("{} < 1", "Invalid operand"), ("1 && true", "Invalid operand"), ("!1", "Invalid operand"),
+    ('!"true"', None), ("-[1]", "Invalid operand"), ("var.n + 1", None), ("[1] == [1]", None),
+    ("length(var.n) > 0 && var.n != null", None), ("upper(var.n) + 1", None),
+])
+def test_static_type_checks(module_dir, expr, summary):
+    text = f'variable "n" {{}}\noutput "o" {{\n  value = {expr}\n}}\n'
+    assert summaries(module_dir, text) == ([summary] if summary else [])
+
+
 def test_aliased_providers_are_distinct(module_dir):
     assert summaries(module_dir, 'provider "aws" {}\nprovider "aws" {\n  alias = "west"\n}\n'
                                  'resource "aws_a" "b" {\n  provider = aws.west\n}\n') == []
