@@ -26,7 +26,7 @@ import sys
 from .check import STAND_IN, check_tree
 from .config.lockfile import check_lock_consistency, load_lockfile
 from .config.validate import validate_module
-from .docs.tfdocs import check_readme, find_readme, inject, render
+from .docs.tfdocs import InjectRefused, check_readme, find_readme, inject, render
 from .fmt import command as fmt_command
 from .hcl.diagnostics import ERROR, WARNING
 from .lint.rules import RULES, run_rules
@@ -117,7 +117,11 @@ def cmd_docs(argv: list[str]) -> int:
     if "--write" in argv:
         readme = find_readme(dirs[0]) or os.path.join(dirs[0], "README.md")
         old = open(readme, encoding="utf-8").read() if os.path.isfile(readme) else ""
-        new = inject(old, render(res.module, load_lockfile(dirs[0], ".")))
+        try:
+            new = inject(old, render(res.module, load_lockfile(dirs[0], ".")))
+        except InjectRefused as e:
+            sys.stderr.write(f"{readme}: not updated: {e}\n")
+            return 1
         if new != old:
             with open(readme, "w", encoding="utf-8") as fh:
                 fh.write(new)

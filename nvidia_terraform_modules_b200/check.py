@@ -140,7 +140,8 @@ def check_tree(root: str, modules: Optional[list[str]] = None) -> TreeReport:
     try:
         # fmt prints paths relative to where it runs, like the real command
         os.chdir(root)
-        top = sorted({m.split(os.sep)[0] for m in mods}) or ["."]
+        # a module at ROOT itself ("." among the modules) already covers every sub-directory
+        top = ["."] if "." in mods or not mods else sorted({m.split(os.sep)[0] for m in mods})
         fmt = run_fmt(top, recursive=True, check=True, want_diff=True)
     finally:
         os.chdir(cwd)

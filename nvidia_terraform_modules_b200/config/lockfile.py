@@ -17,7 +17,7 @@ from typing import Optional
 
 from ..hcl import ast as A
 from ..hcl.diagnostics import Diagnostic, ERROR, NOTICE, WARNING
-from ..hcl.parser import parse
+from ..hcl.parser import parse_path
 from . import typeexpr
 from .model import Module
 from .versions import Constraints, Version, VersionError, try_parse_constraints
@@ -47,8 +47,7 @@ def load_lockfile(directory: str, display_root: Optional[str] = None) -> Optiona
     if not os.path.isfile(path):
         return None
     disp = os.path.relpath(path, display_root) if display_root else path
-    with open(path, "r", encoding="utf-8", newline="") as fh:
-        body, diags, _ = parse(fh.read(), disp)
+    _, body, diags, _ = parse_path(path, disp)
     lock = LockFile(disp, diags=list(diags))
 
     def bad(summary: str, detail: str, node: A.Node) -> None:

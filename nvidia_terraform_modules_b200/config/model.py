@@ -78,21 +78,26 @@ class Output(Decl):
 
 @dataclass
 class Resource(Decl):
-    mode: str = "managed"     # managed | data
+    mode: str = "managed"     # managed | data | ephemeral
     type: str = ""
     has_count: bool = False
     has_for_each: bool = False
     provider_ref: Optional[str] = None      # provider = google-beta / aws.west
+    scope: Optional[str] = None             # name of the check block a nested data source lives in
 
     @property
     def addr(self) -> str:
-        return ("data." if self.mode == "data" else "") + f"{self.type}.{self.name}"
+        return resource_addr(self.mode, self.type, self.name)
 
     @property
     def implied_provider(self) -> str:
         if self.provider_ref:
             return self.provider_ref.split(".")[0]
         return self.type.split("_", 1)[0]
+
+
+def resource_addr(mode: str, typ: str, name: str) -> str:
+    return ("" if mode == "managed" else mode + ".") + f"{typ}.{name}"
 
 
 @dataclass
@@ -330,9 +335,14 @@ class _Loader:
                       f.path, b, "structure")
         for a in asserts:
             self.condition_block(f, a)
-        if len(b.body.blocks_of("data")) > 1:
+        nested = [d for d in b.body.blocks_of("data") if len(d.labels) == 2]
+        if len(nested) > 1:
             self.diag(ERROR, "Multiple nested data resources",
                       "Check blocks can only contain one nested data resource.", f.path, b, "structure")
+        for d in nested[:1]:
+            # the scoped data source shares the module's data-source namespace, but only
+            # its own check block may refer to it
+            self._resource(f, d, "data", scope=b.labels[0].value)
 
     def block_variable(self, f: SourceFile, b: A.Block) -> None:
         name = b.labels[0].value
@@ -500,22 +510,33 @@ class _Loader:
                           f"Blocks of type \"{blk.type}\" are not expected here.", f.path, blk, "structure")
         self.m.module_calls[name] = mc
 
-    def _resource(self, f: SourceFile, b: A.Block, mode: str) -> None:
+    def _resource(self, f: SourceFile, b: A.Block, mode: str, scope: Optional[str] = None) -> None:
         typ, name = b.labels[0].value, b.labels[1].value
-        word = "data source" if mode == "data" else "resource"
-        if not self.check_name(f, b, typ, f"{word} type name" if mode == "managed" else "data source name"):
+        word = {"data": "data source", "ephemeral": "ephemeral resource"}.get(mode, "resource")
+        if not self.check_name(f, b, typ, f"{word} type name" if mode != "data" else "data source name"):
             return
         if not self.check_name(f, b, name, f"{word} name"):
             return
-        r = Resource(name, f.path, b.pos.line, block=b, mode=mode, type=typ)
-        kind = "data" if mode == "data" else "resource"
+        r = Resource(name, f.path, b.pos.line, block=b, mode=mode, type=typ, scope=scope)
+        kind = {"data": "data", "ephemeral": "ephemeral"}.get(mode, "resource")
         if self.duplicate(f, b, self.m.resources, r.addr,
                           f"Duplicate {kind} \"{typ}\" configuration",
                           f"A {typ} {word} named \"{name}\" was already declared at {{prev}}. "
                           f"Resource names must be unique per type in each module."):
             return
         attrs = b.body.attributes
-        r.has_count, r.has_for_each = self._count_for_each(f, b)
+        if scope is not None:
+            for meta in ("count", "for_each"):
+                if meta in attrs:
+                    self.diag(ERROR, f"Invalid \"{meta}\" attribute",
+                              "The \"count\" and \"for_each\" meta-arguments are not supported within nested "
+                              "data blocks.", f.path, attrs[meta], "structure")
+            for blk in b.body.blocks_of("lifecycle"):
+                self.diag(ERROR, "Invalid lifecycle block",
+                          "Nested data blocks do not support \"lifecycle\" blocks as the lifecycle is managed "
+                          "by the containing block.", f.path, blk, "structure")
+        else:
+            r.has_count, r.has_for_each = self._count_for_each(f, b)
         if "provider" in attrs:
             e = attrs["provider"].expr
             if isinstance(e, A.ScopeTraversal) and len(e.steps) <= 1 and all(s.kind == "attr" for s in e.steps):
@@ -549,11 +570,11 @@ class _Loader:
                     self.diag(ERROR, "Invalid ignore_changes ruleset",
                               "The ignore_changes argument must be either a list of attribute names or the "
                               "special keyword \"all\".", f.path, ic.expr, "structure")
-            elif blk.type in ("provisioner", "connection") and mode == "data":
-                self.diag(ERROR, "Unsupported block type" if blk.type == "connection"
+            elif blk.type in ("provisioner", "connection") and mode != "managed":
+                self.diag(ERROR, "Unsupported block type" if blk.type == "connection" or mode == "ephemeral"
                           else "Data resources do not have provisioners",
-                          "Data resources do not have provisioners." if blk.type == "provisioner" else
-                          f"Blocks of type \"{blk.type}\" are not expected here.", f.path, blk, "structure")
+                          "Data resources do not have provisioners." if blk.type == "provisioner" and mode == "data"
+                          else f"Blocks of type \"{blk.type}\" are not expected here.", f.path, blk, "structure")
             elif blk.type == "provisioner":
                 if len(blk.labels) != 1:
                     self.diag(ERROR, "Missing type for provisioner" if not blk.labels
@@ -600,6 +621,9 @@ class _Loader:
 
     def block_data(self, f: SourceFile, b: A.Block) -> None:
         self._resource(f, b, "data")
+
+    def block_ephemeral(self, f: SourceFile, b: A.Block) -> None:
+        self._resource(f, b, "ephemeral")
 
     def block_provider(self, f: SourceFile, b: A.Block) -> None:
         name = b.labels[0].value
@@ -725,7 +749,11 @@ def _signature(directory: str) -> tuple:
         return ()
     sig = []
     for n in names:
-        st = os.stat(os.path.join(directory, n))
+        try:
+            st = os.stat(os.path.join(directory, n))
+        except OSError:                      # dangling symlink: reported when the file is read
+            sig.append((n, 0, -1))
+            continue
         sig.append((n, st.st_mtime_ns, st.st_size))
     return tuple(sig)
 

@@ -26,14 +26,14 @@ interface.  The summary line this command prints says so every time.
 from __future__ import annotations
 
 import os
-from dataclasses import dataclass, field
+from dataclasses import dataclass, field, replace
 from typing import Optional
 
 from ..hcl import ast as A
 from ..hcl.diagnostics import Diagnostic, ERROR, WARNING, has_errors
-from ..hcl.parser import parse
+from ..hcl.parser import parse_path
 from . import functions, kinds, typeexpr
-from .model import Module, ModuleCall, Resource, SourceFile, load_module
+from .model import Module, ModuleCall, Resource, SourceFile, load_module, resource_addr
 
 _PATH_ATTRS = {"module", "root", "cwd"}
 _TERRAFORM_ATTRS = {"workspace", "applying"}
@@ -47,16 +47,14 @@ class Ctx:
     self_ok: bool = False         # "self" is available (provisioner, connection, postcondition)
     names: frozenset = frozenset()    # for-expression / dynamic-block iterator names in scope
     where: str = "module"         # wording: which kind of block we are in
+    check: Optional[str] = None   # inside this check block: its nested data source is visible
+    destroy: bool = False         # inside a destroy-time provisioner
 
     def with_names(self, *names: Optional[str]) -> "Ctx":
-        return Ctx(self.file, self.count, self.each, self.self_ok,
-                   self.names | {n for n in names if n}, self.where)
+        return replace(self, names=self.names | {n for n in names if n})
 
     def but(self, **kw) -> "Ctx":
-        d = dict(file=self.file, count=self.count, each=self.each, self_ok=self.self_ok,
-                 names=self.names, where=self.where)
-        d.update(kw)
-        return Ctx(**d)
+        return replace(self, **kw)
 
 
 @dataclass
@@ -179,9 +177,13 @@ class Validator:
         self.body(b.body, ctx, skip={"alias", "version"})
 
     def visit_check(self, f: SourceFile, b: A.Block) -> None:
-        ctx = Ctx(f.path, where="check")
+        name = b.labels[0].value if b.labels else None
+        ctx = Ctx(f.path, where="check", check=name)
         for blk in b.body.blocks:
-            self.body(blk.body, ctx)
+            if blk.type == "data":
+                self._resource(f, blk, "data", ctx)
+            else:
+                self.body(blk.body, ctx)
 
     def visit_module(self, f: SourceFile, b: A.Block) -> None:
         mc = self.m.module_calls.get(b.labels[0].value) if b.labels else None
@@ -233,14 +235,17 @@ class Validator:
     def visit_data(self, f: SourceFile, b: A.Block) -> None:
         self._resource(f, b, "data")
 
-    def _resource(self, f: SourceFile, b: A.Block, mode: str) -> None:
+    def visit_ephemeral(self, f: SourceFile, b: A.Block) -> None:
+        self._resource(f, b, "ephemeral")
+
+    def _resource(self, f: SourceFile, b: A.Block, mode: str, outer: Optional[Ctx] = None) -> None:
         if len(b.labels) != 2:
             return
-        addr = ("data." if mode == "data" else "") + f"{b.labels[0].value}.{b.labels[1].value}"
+        addr = resource_addr(mode, b.labels[0].value, b.labels[1].value)
         r = self.m.resources.get(addr)
         if r is None or r.block is not b:
             return
-        base = Ctx(f.path, where="resource" if mode == "managed" else "data")
+        base = (outer or Ctx(f.path)).but(where="resource" if mode == "managed" else mode)
         ctx = base.but(count=r.has_count, each=r.has_for_each)
         self._owner = addr
         try:
@@ -261,10 +266,56 @@ class Validator:
         for blk in b.body.blocks:
             if blk.type == "lifecycle":
                 self.lifecycle(blk, ctx)
-            elif blk.type in ("provisioner", "connection"):
-                self.body(blk.body, ctx.but(self_ok=True, where="provisioner"))
+            elif blk.type == "provisioner":
+                self.provisioner(blk, ctx)
+            elif blk.type == "connection":
+                # a resource-level connection is shared by every provisioner; it is held to
+                # the destroy-time rule as soon as one of them runs at destroy time
+                destroy = any(self._when(p) == "destroy" for p in b.body.blocks_of("provisioner"))
+                self.body(blk.body, ctx.but(self_ok=True, where="provisioner", destroy=destroy))
             else:
                 self.nested(blk, ctx)
+
+    _KEYWORDS = {"when": ("create", "destroy"), "on_failure": ("continue", "fail")}
+
+    @staticmethod
+    def _keyword(e: A.Expr) -> Optional[str]:
+        """``destroy`` or the deprecated ``"destroy"``: the bare word, else None."""
+        if isinstance(e, A.ScopeTraversal) and not e.steps:
+            return e.root
+        if isinstance(e, A.Template) and not e.heredoc:
+            return e.literal_value()
+        return None
+
+    def _when(self, blk: A.Block) -> Optional[str]:
+        attr = blk.body.attributes.get("when")
+        return self._keyword(attr.expr) if attr is not None else None
+
+    def provisioner(self, blk: A.Block, ctx: Ctx) -> None:
+        """``when`` and ``on_failure`` take bare keywords, not expressions; everything else
+        goes to the provisioner plugin and may use ``self``."""
+        inner = ctx.but(self_ok=True, where="provisioner", destroy=self._when(blk) == "destroy")
+        for item in blk.body.items:
+            if isinstance(item, A.Block):
+                if item.type == "connection":
+                    self.body(item.body, inner)
+                else:
+                    self.nested(item, inner)
+                continue
+            allowed = self._KEYWORDS.get(item.name)
+            if allowed is None:
+                self.attr_value(item, inner)
+                continue
+            if isinstance(item.expr, A.Template) and self._keyword(item.expr) is not None:
+                self.diag(WARNING, "Quoted keywords are deprecated",
+                          "In this context, keywords are expected literally rather than in quotes. Terraform 0.11 "
+                          "and earlier required quotes, but quoted keywords are now deprecated and will be removed "
+                          "in a future version of Terraform. Remove the quotes surrounding this keyword to silence "
+                          "this warning.", ctx, item.expr, "deprecated")
+            if self._keyword(item.expr) not in allowed:
+                self.diag(ERROR, f"Invalid \"{item.name}\" keyword",
+                          f"The \"{item.name}\" argument requires one of the following keywords: "
+                          f"{allowed[0]} or {allowed[1]}.", ctx, item.expr, "structure")
 
     def lifecycle(self, blk: A.Block, ctx: Ctx) -> None:
         for name, attr in blk.body.attributes.items():
@@ -409,9 +460,7 @@ class Validator:
     @staticmethod
     def _has_key(t: A.ScopeTraversal) -> bool:
         """Does the traversal index the resource/module it names?"""
-        n = 3 if t.root == "data" else 2
-        if t.root in ("module",):
-            n = 2
+        n = 3 if t.root in ("data", "ephemeral") else 2
         return len(t.steps) >= n and t.steps[n - 1].kind == "index"
 
     def call(self, call: A.FunctionCall, ctx: Ctx) -> None:
@@ -438,6 +487,15 @@ class Validator:
 
         def first_attr() -> Optional[str]:
             return steps[0].value if steps and steps[0].kind == "attr" else None
+
+        if ctx.destroy and not (root in ("self", "path", "terraform")
+                                or (root, first_attr(), len(steps)) in (("count", "index", 1), ("each", "key", 1))):
+            self.diag(ERROR, "Invalid reference from destroy provisioner",
+                      "Destroy-time provisioners and their connection configurations may only reference "
+                      "attributes of the related resource, via 'self', 'count.index', or 'each.key'.\n\n"
+                      "References to other resources during the destroy phase can cause dependency cycles "
+                      "and interact poorly with create_before_destroy.", ctx, t, "destroy-provisioner")
+            return
 
         if root == "var":
             name = first_attr()
@@ -469,13 +527,14 @@ class Validator:
                     self.edges.setdefault(self._owner, set()).add(f"local.{name}")
         elif root == "module":
             self.module_ref(t, ctx, keyed)
-        elif root == "data":
+        elif root in ("data", "ephemeral"):
             if len(steps) < 2 or steps[0].kind != "attr" or steps[1].kind != "attr":
+                what = "data source" if root == "data" else "ephemeral resource"
                 self.diag(ERROR, "Invalid reference",
-                          "The \"data\" object must be followed by two attribute names: the data source type "
+                          f"The \"{root}\" object must be followed by two attribute names: the {what} type "
                           "and the resource name.", ctx, t, "reference")
                 return
-            self.resource_ref(t, ctx, "data", steps[0].value, steps[1].value, steps[2:], keyed)
+            self.resource_ref(t, ctx, root, steps[0].value, steps[1].value, steps[2:], keyed)
         elif root == "count":
             name = first_attr()
             if not ctx.count:
@@ -529,12 +588,16 @@ class Validator:
 
     def resource_ref(self, t: A.ScopeTraversal, ctx: Ctx, mode: str, typ: str, name: str,
                      rest: list[A.Step], keyed: bool) -> None:
-        addr = ("data." if mode == "data" else "") + f"{typ}.{name}"
+        addr = resource_addr(mode, typ, name)
         r: Optional[Resource] = self.m.resources.get(addr)
         if r is None:
-            kind = "data resource" if mode == "data" else "managed resource"
             self.diag(ERROR, "Reference to undeclared resource",
-                      f"A {kind} \"{typ}\" \"{name}\" has not been declared in the root module.",
+                      f"A {mode} resource \"{typ}\" \"{name}\" has not been declared in the root module.",
+                      ctx, t, "undeclared-resource")
+            return
+        if r.scope is not None and r.scope != ctx.check:
+            self.diag(ERROR, "Reference to scoped resource",
+                      f"The referenced {mode} resource \"{typ}\" \"{name}\" is not available from this context.",
                       ctx, t, "undeclared-resource")
             return
         self.used_resources.add(addr)
@@ -613,8 +676,7 @@ def check_tfvars(m: Module) -> list[Diagnostic]:
             continue
         path = os.path.join(m.dir, name)
         disp = os.path.join(os.path.dirname(m.files[0].path), name) if m.files else path
-        with open(path, "r", encoding="utf-8", newline="") as fh:
-            body, pd, _ = parse(fh.read(), disp)
+        _, body, pd, _ = parse_path(path, disp)
         diags.extend(pd)
         for item in body.items:
             if isinstance(item, A.Block):

@@ -452,32 +452,80 @@ BEGIN_MARK = "<!-- BEGIN_TF_DOCS -->"
 END_MARK = "<!-- END_TF_DOCS -->"
 
 
+class InjectRefused(ValueError):
+    """The README has no markers and no single, unambiguous generated region."""
+
+
+_HEADING = re.compile(r"^##\s+(\w+)\s*$")
+
+
+def _generated_sections(lines: list[str]) -> list[tuple[int, int, int]]:
+    """``(heading, generated_end, section_end)`` line indices of every section that
+    terraform-docs evidently wrote: a ``## Requirements``-style heading followed,
+    after blank lines only, by a table whose first header cell is ``Name`` or by the
+    one-line ``No inputs.`` sentence.  ``generated_end`` is one past that table or
+    sentence; ``section_end`` is the next heading of any level (or end of file).  A
+    heading of the same name over hand-written prose is not in the list."""
+    found = []
+    for i, ln in enumerate(lines):
+        m = _HEADING.match(ln)
+        if not m or m.group(1) not in SECTIONS:
+            continue
+        j = i + 1
+        while j < len(lines) and lines[j].strip() == "":
+            j += 1
+        if j >= len(lines):
+            continue
+        if re.match(r"^No [a-z ]+\.\s*$", lines[j]):
+            gen_end = j + 1
+        elif lines[j].lstrip().startswith("|") and _split_row(lines[j])[:1] == ["Name"]:
+            gen_end = j
+            while gen_end < len(lines) and lines[gen_end].lstrip().startswith("|"):
+                gen_end += 1
+        else:
+            continue
+        sec_end = gen_end
+        while sec_end < len(lines) and not lines[sec_end].startswith("#"):
+            sec_end += 1
+        found.append((i, gen_end, sec_end))
+    return found
+
+
 def inject(readme_text: str, tables: str) -> str:
-    """Put freshly rendered tables into a README, the three ways terraform-docs'
-    "inject" mode knows: between BEGIN/END markers when present; else in place of
-    the existing run of generated sections (from the first ``## Requirements``-style
-    heading to the end of the last generated table); else appended."""
+    """Put freshly rendered tables into a README.
+
+    * Between ``<!-- BEGIN_TF_DOCS -->`` / ``<!-- END_TF_DOCS -->`` when the README has
+      them -- terraform-docs' "inject" mode.
+    * Without markers terraform-docs only ever appends.  The reference's READMEs were
+      made by pasting its output, without markers, so one more case is handled: when
+      the README holds exactly ONE unbroken run of generated sections (see
+      ``_generated_sections``; nothing but blank lines between one section's table and
+      the next section's heading) that run is replaced, and whatever follows its last
+      table is kept.  Sections named "Requirements", "Resources", ... that hold
+      hand-written prose are never touched.
+    * No generated section at all: the tables are appended between markers, as
+      terraform-docs does.
+    * Generated sections split up by hand-written text: ``InjectRefused`` -- there is
+      no single region to replace, and guessing would delete somebody's prose.
+    """
     tables = tables.rstrip("\n") + "\n"
     if BEGIN_MARK in readme_text and END_MARK in readme_text:
         head, rest = readme_text.split(BEGIN_MARK, 1)
         _, tail = rest.split(END_MARK, 1)
         return f"{head}{BEGIN_MARK}\n{tables}{END_MARK}{tail}"
     lines = readme_text.split("\n")
-    starts = [i for i, ln in enumerate(lines)
-              if re.match(r"^##\s+(\w+)\s*$", ln) and re.match(r"^##\s+(\w+)\s*$", ln).group(1) in SECTIONS]
-    if not starts:
+    secs = _generated_sections(lines)
+    if not secs:
         sep = "" if readme_text.endswith("\n\n") or not readme_text else ("\n" if readme_text.endswith("\n") else "\n\n")
-        return readme_text + sep + tables
-    first = starts[0]
-    # the generated run ends where the last generated section's table (or its
-    # one-line "No ..." sentence) ends
-    end = starts[-1] + 1
-    while end < len(lines) and not lines[end].startswith("#"):
-        end += 1
-    while end > starts[-1] + 1 and lines[end - 1].strip() == "":
-        end -= 1
-    tail = lines[end:]
-    out = lines[:first] + tables.rstrip("\n").split("\n") + tail
+        return f"{readme_text}{sep}{BEGIN_MARK}\n{tables}{END_MARK}\n"
+    for (_, gen_end, sec_end), (nxt, _, _) in zip(secs, secs[1:]):
+        if sec_end != nxt or any(ln.strip() for ln in lines[gen_end:sec_end]):
+            at = next((k for k in range(gen_end, nxt) if lines[k].strip()), gen_end)
+            raise InjectRefused(
+                f"generated sections are interrupted by other text at line {at + 1}; put "
+                f"{BEGIN_MARK} and {END_MARK} around the region to regenerate")
+    first, end = secs[0][0], secs[-1][1]
+    out = lines[:first] + tables.rstrip("\n").split("\n") + lines[end:]
     text = "\n".join(out)
     if readme_text.endswith("\n") and not text.endswith("\n"):
         text += "\n"

@@ -140,7 +140,12 @@ def run_fmt(targets: Iterable[str], *, recursive: bool = False, write: bool = Tr
         else:
             res.diags.append(Diagnostic("error", f"No file or directory at {target}", file=target,
                                         rule="fmt-target"))
+    seen: set[str] = set()
     for path in files:
+        real = os.path.normpath(path)
+        if real in seen:                 # overlapping targets ("." and "sub") name a file once
+            continue
+        seen.add(real)
         src, body, pdiags, tokens = parse_path(path, _display(path))
         res.checked.append(_display(path))
         res.bytes_checked += len(src.encode("utf-8"))

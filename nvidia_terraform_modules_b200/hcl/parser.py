@@ -904,14 +904,39 @@ def parse_path(path: str, display: str) -> tuple[str, A.Body, list[Diagnostic], 
     times -- fmt, the module that owns it, modules that call that module -- and
     they all share one parse.  Callers must treat the result as read-only;
     ``fmt`` restores the ``spaces_before`` values it touches."""
-    st = os.stat(path)
+    try:
+        st = os.stat(path)
+    except OSError as e:
+        return _unreadable(display, e)
     key = (os.path.abspath(path), display, st.st_mtime_ns, st.st_size)
     hit = _FILE_CACHE.get(key)
     if hit is None:
-        with open(path, "r", encoding="utf-8", newline="") as fh:
-            src = fh.read()
+        try:
+            with open(path, "rb") as fh:
+                raw = fh.read()
+        except OSError as e:
+            return _unreadable(display, e)
+        try:
+            src = raw.decode("utf-8")
+        except UnicodeDecodeError as e:
+            # HCL's scanner reports this for the one file and carries on with the rest
+            line = raw.count(b"\n", 0, e.start) + 1
+            col = e.start - (raw.rfind(b"\n", 0, e.start) + 1) + 1
+            diag = Diagnostic(ERROR, "Invalid character encoding",
+                              "All input files must be UTF-8 encoded. Ensure that UTF-8 encoding is selected "
+                              "in your editor.", display, line, col, "syntax")
+            return "", A.Body(), [diag], []
         body, diags, tokens = parse(src, display)
         if len(_FILE_CACHE) > 4096:
             _FILE_CACHE.clear()
         hit = _FILE_CACHE[key] = (src, body, diags, tokens)
     return hit
+
+
+def _unreadable(display: str, err: OSError) -> tuple[str, A.Body, list[Diagnostic], list[Token]]:
+    """A file that cannot be opened (dangling symlink, permissions) is that file's
+    problem only: one error diagnostic, no tokens, and the run goes on."""
+    why = err.strerror or str(err)
+    diag = Diagnostic(ERROR, "Failed to read file", f"The file \"{display}\" could not be read: {why}.",
+                      display, 0, 0, "syntax")
+    return "", A.Body(), [diag], []

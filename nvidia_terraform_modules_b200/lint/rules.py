@@ -298,8 +298,11 @@ def eof_newline(c: LintContext):
         extra = []
     base = os.path.dirname(c.m.files[0].path) if c.m.files else c.m.dir
     for n in extra:
-        with open(os.path.join(c.m.dir, n), "r", encoding="utf-8", newline="") as fh:
-            src = fh.read()
+        try:
+            with open(os.path.join(c.m.dir, n), "r", encoding="utf-8", newline="") as fh:
+                src = fh.read()
+        except (OSError, UnicodeDecodeError):
+            continue                      # validate reports the unreadable file
         if src and not src.endswith("\n"):
             yield Diagnostic(NOTICE, "No newline at end of file", "", os.path.join(base, n),
                              src.count("\n") + 1, 0, "eof-newline")
@@ -589,8 +592,11 @@ def helper_script(c: LintContext):
     base = os.path.dirname(c.m.files[0].path) if c.m.files else c.m.dir
     hcl_text = "\n".join(f.src for f in c.m.files)
     for name in scripts:
-        with open(os.path.join(c.m.dir, name), "r", encoding="utf-8", errors="replace") as fh:
-            lines = fh.read().split("\n")
+        try:
+            with open(os.path.join(c.m.dir, name), "r", encoding="utf-8", errors="replace") as fh:
+                lines = fh.read().split("\n")
+        except OSError:
+            continue
         disp = os.path.join(base, name)
         if name not in hcl_text:
             yield Diagnostic(WARNING, f"{name} is not referenced by any .tf file of this module",

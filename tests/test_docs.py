@@ -1,6 +1,9 @@
 """README tables: generation in terraform-docs' layout and drift detection."""
+import pytest
+
 from nvidia_terraform_modules_b200.config.model import load_module
-from nvidia_terraform_modules_b200.docs.tfdocs import BEGIN_MARK, END_MARK, check_readme, inject, parse_readme, render
+from nvidia_terraform_modules_b200.docs.tfdocs import (BEGIN_MARK, END_MARK, InjectRefused, check_readme, inject,
+                                                       parse_readme, render)
 
 FILES = {
     "versions.tf": 'terraform {\n  required_version = ">= 1.2.4"\n  required_providers {\n    aws = {\n'
@@ -133,5 +136,33 @@ def test_inject_between_markers_and_append(module_dir):
     fresh = render(m)
     marked = f"# T\n\n{BEGIN_MARK}\nold junk\n{END_MARK}\n\nfooter\n"
     assert inject(marked, fresh) == f"# T\n\n{BEGIN_MARK}\n{fresh}{END_MARK}\n\nfooter\n"
-    assert inject("# T\n\nprose\n", fresh) == "# T\n\nprose\n\n" + fresh
-    assert inject("", fresh) == fresh
+    # no markers and nothing generated yet: appended between markers, like terraform-docs
+    wrapped = f"{BEGIN_MARK}\n{fresh}{END_MARK}\n"
+    assert inject("# T\n\nprose\n", fresh) == "# T\n\nprose\n\n" + wrapped
+    assert inject("", fresh) == wrapped
+    assert inject(inject("# T\n", fresh), fresh) == inject("# T\n", fresh)      # and then idempotent
+
+
+def test_inject_leaves_hand_written_sections_alone(module_dir):
+    """Advisor finding, round 1: a prose "## Requirements" and a "## Usage" between it
+    and the generated tables used to be deleted by `docs --write`."""
+    _, m = module(module_dir)
+    fresh = render(m)
+    stale = fresh.replace("| `true` | no |", "| `false` | no |")
+    prose = "# T\n\n## Requirements\n\nYou need an AWS account.\n\n## Usage\n\nrun it\n\n"
+    tail = "\nSee also the wiki.\n\n## Resources\n\nLinks, not a table.\n"
+    after = inject(prose + stale + tail, fresh)
+    assert after == prose + fresh + tail
+    assert inject(after, fresh) == after
+
+
+def test_inject_refuses_when_generated_sections_are_split_by_prose(module_dir):
+    _, m = module(module_dir)
+    fresh = render(m)
+    cut = fresh.index("## Inputs")
+    split = fresh[:cut] + "## Notes\n\nhand-written, between two generated tables\n\n" + fresh[cut:]
+    with pytest.raises(InjectRefused, match="interrupted by other text at line"):
+        inject("# T\n\n" + split, fresh)
+    loose = fresh[:cut] + "a stray paragraph\n\n" + fresh[cut:]
+    with pytest.raises(InjectRefused):
+        inject(loose, fresh)
