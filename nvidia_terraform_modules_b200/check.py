@@ -14,6 +14,7 @@ import time
 from dataclasses import dataclass, field
 from typing import Optional
 
+from .config import tfversion
 from .config.lockfile import check_lock_consistency, load_lockfile
 from .config.validate import ValidateResult, validate_module
 from .docs.tfdocs import check_readme, find_readme
@@ -21,7 +22,8 @@ from .fmt.command import FmtResult, run_fmt
 from .hcl.diagnostics import Diagnostic, ERROR, WARNING, NOTICE
 from .lint.rules import run_rules
 
-STAND_IN = ("stand-in: restated from the published behaviour of Terraform / hashicorp-hcl; "
+STAND_IN = ("stand-in: restated from the published behaviour of Terraform "
+            f"{tfversion.text(tfversion.OLDEST)}-{tfversion.text(tfversion.NEWEST)} / hashicorp-hcl v2; "
             "the real `terraform` binary is not available offline, parity is unpinned")
 
 
@@ -54,6 +56,8 @@ class ModuleReport:
     lock: list[Diagnostic] = field(default_factory=list)
     docs: list[Diagnostic] = field(default_factory=list)
     counts: dict = field(default_factory=dict)
+    terraform_version: str = ""             # the release validate restated for this module
+    terraform_version_source: str = ""
 
     def all(self) -> list[Diagnostic]:
         return self.validate + self.lint + self.lock + self.docs
@@ -109,15 +113,18 @@ class TreeReport:
                        "fmt_differing": len(self.fmt.changed)},
             "baseline_configs": self.baseline_configs(),
             "fmt": {"checked": self.fmt.checked, "changed": self.fmt.changed},
-            "modules": [{"path": m.path, "counts": m.counts,
+            "modules": [{"path": m.path, "counts": m.counts, "terraform_version": m.terraform_version,
+                         "terraform_version_source": m.terraform_version_source,
                          "diagnostics": [d.to_dict() for d in m.all()]} for m in self.modules],
         }
 
 
-def check_module(root: str, rel: str) -> tuple[ModuleReport, ValidateResult]:
+def check_module(root: str, rel: str, terraform_version: Optional[str] = None) -> tuple[ModuleReport, ValidateResult]:
     directory = os.path.normpath(os.path.join(root, rel))
-    result = validate_module(directory, root)
+    result = validate_module(directory, root, terraform_version)
     rep = ModuleReport(rel)
+    rep.terraform_version = result.module.restated.text
+    rep.terraform_version_source = result.module.restated.describe()
     rep.validate = result.diags
     rep.lint = run_rules(result)
     children = tuple(c for c in result.validator.children.values() if c is not None)
@@ -133,7 +140,8 @@ def check_module(root: str, rel: str) -> tuple[ModuleReport, ValidateResult]:
     return rep, result
 
 
-def check_tree(root: str, modules: Optional[list[str]] = None) -> TreeReport:
+def check_tree(root: str, modules: Optional[list[str]] = None,
+               terraform_version: Optional[str] = None) -> TreeReport:
     t0 = time.perf_counter()
     mods = modules if modules is not None else discover_modules(root)
     cwd = os.getcwd()
@@ -145,6 +153,6 @@ def check_tree(root: str, modules: Optional[list[str]] = None) -> TreeReport:
         fmt = run_fmt(top, recursive=True, check=True, want_diff=True)
     finally:
         os.chdir(cwd)
-    reports = [check_module(root, rel)[0] for rel in mods]
+    reports = [check_module(root, rel, terraform_version)[0] for rel in mods]
     nbytes = fmt.bytes_checked
     return TreeReport(root, fmt, reports, time.perf_counter() - t0, nbytes)

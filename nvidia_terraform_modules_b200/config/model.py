@@ -20,7 +20,8 @@ from ..hcl.diagnostics import Diagnostic, ERROR, WARNING, has_errors
 from ..hcl.parser import parse_path
 from ..hcl.scanner import is_valid_identifier
 from ..hcl.tokens import Token
-from . import typeexpr
+from . import tfversion, typeexpr
+from .tfversion import Restated
 from .versions import Constraints, try_parse_constraints
 
 _BAD_NAME = ("A name must start with a letter or underscore and may contain only letters, digits, "
@@ -160,6 +161,8 @@ class Module:
     diags: list[Diagnostic] = field(default_factory=list)
     broken_files: set = field(default_factory=set)       # files with syntax errors
     display_root: Optional[str] = None                   # paths in messages are relative to this
+    restated: Restated = field(default_factory=lambda: Restated(tfversion.NEWEST, "default"))
+    experiments: set = field(default_factory=set)        # active language experiments
 
     def used_provider_names(self) -> dict[str, list[Resource]]:
         out: dict[str, list[Resource]] = {}
@@ -170,10 +173,32 @@ class Module:
 
 # ---------------------------------------------------------------------------
 class _Loader:
-    def __init__(self, directory: str, display_root: Optional[str] = None):
+    def __init__(self, directory: str, display_root: Optional[str] = None, restated: Optional[Restated] = None):
         self.m = Module(directory)
         self.m.display_root = display_root
         self.root = display_root
+        self.forced = restated
+
+    @property
+    def v(self) -> Restated:
+        return self.m.restated
+
+    def needs(self, feature: str, what: str) -> str:
+        """The sentence appended to Terraform's own wording when something is refused
+        only because of the release being restated."""
+        return (f"\n\n({what} needs Terraform {tfversion.text(tfversion.SINCE[feature])} or later; this run "
+                f"restates {self.v.describe()}.)")
+
+    def sniff_required_versions(self) -> list[tuple[str, str]]:
+        found = []
+        for f in self.m.files:
+            for item in f.body.items:
+                if isinstance(item, A.Block) and item.type == "terraform":
+                    attr = item.body.attributes.get("required_version")
+                    val = typeexpr.literal_value(attr.expr) if attr is not None else None
+                    if isinstance(val, str):
+                        found.append((val, f"{f.path}:{attr.pos.line}"))
+        return found
 
     def diag(self, sev: str, summary: str, detail: str, file: str, node, rule: str) -> None:
         line = node.pos.line if isinstance(node, A.Node) else int(node)
@@ -202,6 +227,14 @@ class _Loader:
             self.m.files.append(SourceFile(disp, src, body, tokens))
             if has_errors(diags):
                 self.m.broken_files.add(disp)
+        self.m.restated = self.forced or tfversion.from_required_version(self.sniff_required_versions())
+        # experiments apply to the whole module, whichever file happens to be read first
+        for f in self.m.files:
+            if f.path not in self.m.broken_files:
+                for b in f.body.blocks_of("terraform"):
+                    for it in self._experiment_keywords(b):
+                        if it.root == "module_variable_optional_attrs" and not self.v.has("optional-attributes"):
+                            self.m.experiments.add(it.root)
         for f in self.m.files:
             # a file that does not parse contributes no declarations: what the
             # recovering parser salvaged would only produce follow-on noise
@@ -217,6 +250,12 @@ class _Loader:
                           f"An argument named \"{item.name}\" is not expected here.", f.path, item, "structure")
                 continue
             want = TOP_LEVEL_BLOCKS.get(item.type)
+            feature = f"block:{item.type}"
+            if want is not None and feature in tfversion.SINCE and not self.v.has(feature):
+                self.diag(ERROR, "Unsupported block type",
+                          f"Blocks of type \"{item.type}\" are not expected here."
+                          + self.needs(feature, f"A \"{item.type}\" block"), f.path, item, "terraform-version")
+                continue
             if want is None:
                 self.diag(ERROR, "Unsupported block type",
                           f"Blocks of type \"{item.type}\" are not expected here.", f.path, item, "structure")
@@ -245,12 +284,30 @@ class _Loader:
             return False
         return True
 
-    def check_args(self, f: SourceFile, b: A.Block, allowed: set[str], blocks: dict[str, int]) -> None:
+    def check_args(self, f: SourceFile, b: A.Block, allowed: set[str], blocks: dict[str, int],
+                   gates: str = "") -> None:
+        """``gates``: prefix under which tfversion.SINCE lists the arguments and nested
+        blocks of this block type that newer releases added (``"variable"`` ->
+        ``variable:nullable`` ...)."""
+        def too_new(name: str) -> Optional[str]:
+            feature = f"{gates}:{name}"
+            return feature if gates and feature in tfversion.SINCE and not self.v.has(feature) else None
+
         for item in b.body.items:
             if isinstance(item, A.Attribute):
-                if item.name not in allowed:
+                if item.name in allowed and too_new(item.name):
+                    self.diag(ERROR, "Unsupported argument",
+                              f"An argument named \"{item.name}\" is not expected here."
+                              + self.needs(too_new(item.name), f"The \"{item.name}\" argument"),
+                              f.path, item, "terraform-version")
+                elif item.name not in allowed:
                     self.diag(ERROR, "Unsupported argument",
                               f"An argument named \"{item.name}\" is not expected here.", f.path, item, "structure")
+            elif item.type in blocks and too_new(item.type):
+                self.diag(ERROR, "Unsupported block type",
+                          f"Blocks of type \"{item.type}\" are not expected here."
+                          + self.needs(too_new(item.type), f"A \"{item.type}\" block here"),
+                          f.path, item, "terraform-version")
             elif item.type not in blocks:
                 self.diag(ERROR, "Unsupported block type",
                           f"Blocks of type \"{item.type}\" are not expected here.", f.path, item, "structure")
@@ -297,6 +354,29 @@ class _Loader:
                           f.path, node, "structure")
                 return
 
+    @staticmethod
+    def _free_references(expr: A.Expr) -> list[A.ScopeTraversal]:
+        """References in ``expr`` that are not for-expression iterator names."""
+        out: list[A.ScopeTraversal] = []
+
+        def visit(n: A.Node, bound: frozenset) -> None:
+            if isinstance(n, A.ScopeTraversal):
+                if n.root not in bound:
+                    out.append(n)
+                return
+            if isinstance(n, (A.ForExpr, A.TemplateFor)):
+                visit(n.coll, bound)
+                inner = bound | {x for x in (n.key_var, n.val_var) if x}
+                for ch in n.children():
+                    if ch is not n.coll:
+                        visit(ch, inner)
+                return
+            for ch in n.children():
+                visit(ch, bound)
+
+        visit(expr, frozenset())
+        return out
+
     # -- block handlers ----------------------------------------------------
     def block_other(self, f: SourceFile, b: A.Block) -> None:
         pass
@@ -318,11 +398,11 @@ class _Loader:
         self.require(f, b, "from", "to")
 
     def block_import(self, f: SourceFile, b: A.Block) -> None:
-        self.check_args(f, b, {"to", "id", "provider", "for_each"}, {})
+        self.check_args(f, b, {"to", "id", "provider", "for_each"}, {}, gates="import")
         self.require(f, b, "to", "id")
 
     def block_removed(self, f: SourceFile, b: A.Block) -> None:
-        self.check_args(f, b, {"from"}, {"lifecycle": 0, "provisioner": 1})
+        self.check_args(f, b, {"from"}, {"lifecycle": 0, "provisioner": 1}, gates="removed")
         self.require(f, b, "from")
 
     def block_check(self, f: SourceFile, b: A.Block) -> None:
@@ -352,7 +432,7 @@ class _Loader:
             self.diag(ERROR, "Invalid variable name",
                       f"The variable name \"{name}\" is reserved due to its special meaning inside module blocks.",
                       f.path, b, "structure")
-        self.check_args(f, b, VARIABLE_ARGS, {"validation": 0})
+        self.check_args(f, b, VARIABLE_ARGS, {"validation": 0}, gates="variable")
         for vb in b.body.blocks_of("validation"):
             self.condition_block(f, vb)
             cond = vb.body.attributes.get("condition")
@@ -363,6 +443,18 @@ class _Loader:
                     self.diag(ERROR, "Invalid variable validation condition",
                               f"The condition for variable \"{name}\" must refer to var.{name} in order to test "
                               "incoming values.", f.path, cond.expr, "structure")
+            if not self.v.has("validation-refers-to-other-objects"):
+                # until 1.9 a validation rule could see nothing but its own variable
+                for arg, what in (("condition", "condition"), ("error_message", "error message")):
+                    attr = vb.body.attributes.get(arg)
+                    for r in self._free_references(attr.expr) if attr is not None else ():
+                        if not (r.root == "var" and r.steps and r.steps[0].value == name):
+                            self.diag(ERROR, "Invalid reference in variable validation",
+                                      f"The {what} for variable \"{name}\" can only refer to the variable itself, "
+                                      f"using var.{name}."
+                                      + self.needs("validation-refers-to-other-objects",
+                                                   "A validation rule that refers to other objects"),
+                                      f.path, r, "terraform-version")
         if self.duplicate(f, b, self.m.variables, name, "Duplicate variable declaration",
                           f"A variable named \"{name}\" was already declared at {{prev}}. "
                           "Variable names must be unique within a module."):
@@ -374,6 +466,7 @@ class _Loader:
                 v.type = typeexpr.parse_type(attrs["type"].expr)
             except typeexpr.TypeError_ as e:
                 self.diag(ERROR, "Invalid type specification", str(e), f.path, e.node, "type")
+            self.optional_attributes(f, b, attrs["type"].expr)
         if "description" in attrs:
             v.description = self.literal(f, attrs["description"], str, "description")
         if "sensitive" in attrs:
@@ -415,7 +508,7 @@ class _Loader:
         name = b.labels[0].value
         if not self.check_name(f, b, name, "output name"):
             return
-        self.check_args(f, b, OUTPUT_ARGS, {"precondition": 0})
+        self.check_args(f, b, OUTPUT_ARGS, {"precondition": 0}, gates="output")
         for pb in b.body.blocks_of("precondition"):
             self.condition_block(f, pb)
         attrs = b.body.attributes
@@ -560,7 +653,7 @@ class _Loader:
                               "This resource already has a lifecycle block.", f.path, blk, "structure")
                 seen_lifecycle = True
                 self.check_args(f, blk, LIFECYCLE_ARGS if mode == "managed" else set(),
-                                {"precondition": 0, "postcondition": 0})
+                                {"precondition": 0, "postcondition": 0}, gates="lifecycle")
                 for cb in blk.body.blocks:
                     if cb.type in ("precondition", "postcondition"):
                         self.condition_block(f, cb)
@@ -654,8 +747,9 @@ class _Loader:
 
     def block_terraform(self, f: SourceFile, b: A.Block) -> None:
         self.check_args(f, b, {"required_version", "experiments", "language"},
-                        {"required_providers": 0, "backend": 1, "cloud": 0, "provider_meta": 1,
-                         "encryption": 0})
+                        {"required_providers": 0, "backend": 1, "cloud": 0, "provider_meta": 1},
+                        gates="terraform")
+        self.experiments(f, b)
         attrs = b.body.attributes
         if "required_version" in attrs:
             text = self.literal(f, attrs["required_version"], str, "version constraint")
@@ -685,6 +779,54 @@ class _Loader:
         rp_blocks = b.body.blocks_of("required_providers")
         for rp in rp_blocks:
             self.required_providers(f, rp)
+
+    def experiments(self, f: SourceFile, b: A.Block) -> None:
+        """``experiments = [name, ...]``.  Only the one experiment that changes what
+        this checker accepts is judged: optional object attributes, an experiment from
+        0.14 until 1.3 made the (changed) feature part of the language."""
+        for it in self._experiment_keywords(b):
+            if it.root != "module_variable_optional_attrs":
+                continue
+            if self.v.has("optional-attributes"):
+                self.diag(ERROR, "Experiment has concluded",
+                          "Experiment \"module_variable_optional_attrs\" is no longer available. The final "
+                          "feature corresponding to this experiment differs from the experimental form and is "
+                          "available in the Terraform language from Terraform v1.3.0 onwards.",
+                          f.path, it, "terraform-version")
+            else:
+                self.diag(WARNING, "Experimental feature \"module_variable_optional_attrs\" is active",
+                          "Experimental features are subject to breaking changes in future minor or patch "
+                          "releases, based on feedback.\n\nIf you have feedback on the design of this feature, "
+                          "please open a GitHub issue to discuss it.", f.path, it, "terraform-version")
+
+    @staticmethod
+    def _experiment_keywords(b: A.Block) -> list[A.ScopeTraversal]:
+        attr = b.body.attributes.get("experiments")
+        if attr is None or not isinstance(attr.expr, A.TupleCons):
+            return []
+        return [it for it in attr.expr.items if isinstance(it, A.ScopeTraversal) and not it.steps]
+
+    def optional_attributes(self, f: SourceFile, b: A.Block, type_expr: A.Expr) -> None:
+        """Before 1.3 ``optional(...)`` needed the experiment, and took no default."""
+        if self.v.has("optional-attributes"):
+            return
+        calls = [n for n in type_expr.walk() if isinstance(n, A.FunctionCall) and n.name == "optional"]
+        if not calls:
+            return
+        if "module_variable_optional_attrs" not in self.m.experiments:
+            self.diag(ERROR, "Optional object type attributes are experimental",
+                      "This feature is currently an opt-in experiment, subject to change in future releases "
+                      "based on feedback.\n\nActivate the feature for this module by adding "
+                      "module_variable_optional_attrs to the list of active experiments."
+                      + self.needs("optional-attributes", "optional() without the experiment"),
+                      f.path, b, "terraform-version")
+            return
+        for c in calls:
+            if len(c.args) > 1:
+                self.diag(ERROR, "Invalid type specification",
+                          "Optional attribute modifier expects only one argument: the attribute type."
+                          + self.needs("optional-attributes", "A default value inside optional()"),
+                          f.path, c, "terraform-version")
 
     def required_providers(self, f: SourceFile, rp: A.Block) -> None:
         for blk in rp.body.blocks:
@@ -758,13 +900,18 @@ def _signature(directory: str) -> tuple:
     return tuple(sig)
 
 
-def load_module(directory: str, display_root: Optional[str] = None) -> Module:
+def load_module(directory: str, display_root: Optional[str] = None,
+                restated: Optional[Restated] = None) -> Module:
     """Parse every ``*.tf`` file of ``directory`` and build its Module.  The
-    result is shared (and must be treated as read-only) until a file changes."""
-    key = (os.path.abspath(directory), display_root, _signature(directory))
+    result is shared (and must be treated as read-only) until a file changes.
+
+    ``restated`` fixes the Terraform release whose rules apply (a child module is
+    read under its caller's); without it the module's own ``required_version``
+    decides -- see ``tfversion``."""
+    key = (os.path.abspath(directory), display_root, restated, _signature(directory))
     m = _MODULE_CACHE.get(key)
     if m is None:
         if len(_MODULE_CACHE) > 1024:
             _MODULE_CACHE.clear()
-        m = _MODULE_CACHE[key] = _Loader(directory, display_root).load()
+        m = _MODULE_CACHE[key] = _Loader(directory, display_root, restated).load()
     return m

@@ -32,7 +32,7 @@ from typing import Optional
 from ..hcl import ast as A
 from ..hcl.diagnostics import Diagnostic, ERROR, WARNING, has_errors
 from ..hcl.parser import parse_path
-from . import functions, kinds, typeexpr
+from . import functions, kinds, tfversion, typeexpr
 from .model import Module, ModuleCall, Resource, SourceFile, load_module, resource_addr
 
 _PATH_ATTRS = {"module", "root", "cwd"}
@@ -84,7 +84,8 @@ class Validator:
             return None
         if mc.name not in self.children:
             path = os.path.normpath(os.path.join(self.m.dir, mc.source))
-            self.children[mc.name] = load_module(path, self.m.display_root) if os.path.isdir(path) else None
+            self.children[mc.name] = (load_module(path, self.m.display_root, self.m.restated)
+                                      if os.path.isdir(path) else None)
         return self.children[mc.name]
 
     # -- entry ---------------------------------------------------------------
@@ -465,7 +466,32 @@ class Validator:
 
     def call(self, call: A.FunctionCall, ctx: Ctx) -> None:
         name = call.name
+        v = self.m.restated
         if name.startswith("provider::"):
+            if not v.has("provider-defined-functions"):
+                # older HCL stops at the "::" with a syntax error of its own wording; what is
+                # restated here is only that the call is refused
+                self.diag(ERROR, "Provider-defined functions are not available",
+                          f"The call to {name}() uses the provider:: namespace, which needs Terraform "
+                          f"{tfversion.text(tfversion.SINCE['provider-defined-functions'])} or later; this run "
+                          f"restates {v.describe()}.", ctx, call, "terraform-version")
+            return
+        bare = name[len("core::"):] if name.startswith("core::") else name
+        if name.startswith("core::") and not v.has("provider-defined-functions"):
+            self.diag(ERROR, "Call to unknown function", f"There is no function named \"{name}\".\n\n(The core:: "
+                      f"namespace needs Terraform 1.8 or later; this run restates {v.describe()}.)",
+                      ctx, call, "terraform-version")
+            return
+        if functions.lookup(name) is not None and not v.has_function(bare):
+            self.diag(ERROR, "Call to unknown function",
+                      f"There is no function named \"{name}\".\n\n(\"{bare}\" was added in Terraform "
+                      f"{tfversion.text(tfversion.FUNCTION_SINCE[bare])}; this run restates {v.describe()}.)",
+                      ctx, call, "terraform-version")
+            return
+        if bare in functions.REMOVED and v.release < tfversion.LEGACY_FUNCTIONS_REMOVED:
+            self.diag(WARNING, f"The \"{bare}\" function is deprecated",
+                      f"Terraform {v.text} still accepts {bare}(...), and Terraform 0.15 removed it: use "
+                      f"{'tolist([...])' if bare == 'list' else 'tomap({...})'} instead.", ctx, call, "deprecated")
             return
         if functions.lookup(name) is None:
             if name in functions.REMOVED:
@@ -570,6 +596,8 @@ class Validator:
                           "attributes are path.module, path.root, and path.cwd.", ctx, t, "reference")
         elif root == "terraform":
             name = first_attr()
+            if name == "applying" and not self.m.restated.has("terraform.applying"):
+                name = None
             if name not in _TERRAFORM_ATTRS:
                 self.diag(ERROR, "Invalid \"terraform\" attribute",
                           f"The \"terraform\" object does not have an attribute named \"{name}\". The only "
@@ -722,8 +750,12 @@ class ValidateResult:
         return not has_errors(self.diags)
 
 
-def validate_module(directory: str, display_root: Optional[str] = None) -> ValidateResult:
-    m = load_module(directory, display_root)
+def validate_module(directory: str, display_root: Optional[str] = None,
+                    terraform_version: Optional[str] = None) -> ValidateResult:
+    """``terraform_version`` ("1.5", "1.5.7"): the release whose rules apply; by default
+    the lowest one the module's ``required_version`` admits (``tfversion``)."""
+    restated = tfversion.from_flag(terraform_version) if terraform_version else None
+    m = load_module(directory, display_root, restated)
     v = Validator(m)
     diags = list(m.diags)
     if m.broken_files:

@@ -46,7 +46,48 @@ def test_validate_text_and_json(trees):
     assert p.returncode == 1 and data["valid"] is False and data["error_count"] == 2
     assert {d["summary"] for d in data["diagnostics"]} == {"Reference to undeclared input variable",
                                                           "Call to unknown function"}
-    assert data["diagnostics"][0]["range"]["filename"] == "cloud0/outputs.tf"
+    rng = data["diagnostics"][0]["range"]
+    assert rng["filename"] == "outputs.tf"                        # relative to the directory argument
+    assert rng["abs_filename"] == str(trees / "bad" / "cloud0" / "outputs.tf")
+    assert data["terraform_version"] == "1.3" and "required_version" in data["terraform_version_source"]
+
+
+def test_file_names_are_relative_to_the_directory_argument_from_any_cwd(trees, tmp_path):
+    """Round-1 verdict: validating /tmp/x from elsewhere printed ``on ../../tmp/x/main.tf:3``."""
+    elsewhere = tmp_path / "deep" / "er"
+    elsewhere.mkdir(parents=True)
+    bad = trees / "bad" / "cloud0"
+    p = cli(["validate", str(bad)], elsewhere)
+    assert "  on outputs.tf:" in p.stderr and ".." not in p.stderr
+    p = cli(["docs", "--check", str(trees / "clean" / "cloud0")], elsewhere)
+    assert p.returncode == 0 and ".." not in p.stdout
+    p = cli(["lint", "--json", str(bad)], elsewhere)
+    assert {d["file"] for d in json.loads(p.stdout)} <= {"main.tf", "variables.tf", "outputs.tf"}
+    assert all(d["abs_file"] == str(bad / d["file"]) for d in json.loads(p.stdout))
+    # several directories: names stay distinguishable, still no climbing out
+    p = cli(["lint", "--json", str(bad), str(trees / "bad" / "cloud0" / "examples" / "basic")], elsewhere)
+    assert all(not d["file"].startswith("..") for d in json.loads(p.stdout))
+    # a child module outside the directory is the one case that needs "..", as in Terraform
+    p = cli(["check", "--json", str(trees / "bad")], elsewhere)
+    files = {d["file"] for m in json.loads(p.stdout)["modules"] for d in m["diagnostics"]}
+    assert files and all(f.startswith("cloud0/") for f in files)
+
+
+def test_terraform_version_option(trees):
+    mod = trees / "gated"
+    mod.mkdir()
+    (mod / "main.tf").write_text('moved {\n  from = a_b.c\n  to   = a_b.d\n}\nresource "a_b" "d" {}\n')
+    assert cli(["validate", str(mod)], trees).returncode == 0
+    p = cli(["validate", "--terraform-version", "1.0", str(mod)], trees)
+    assert p.returncode == 1 and 'Blocks of type "moved" are not expected here.' in p.stderr
+    assert "needs Terraform 1.1 or later; this run restates Terraform 1.0 (--terraform-version)" in p.stderr
+    assert cli(["validate", "-terraform-version=1.1.9", str(mod)], trees).returncode == 0
+    p = cli(["validate", "--terraform-version", "latest", str(mod)], trees)
+    assert p.returncode == 1 and "not a Terraform version" in p.stderr
+    p = cli(["check", "--terraform-version", "1.0", str(mod)], trees)
+    assert p.returncode == 1 and "validated as Terraform 1.0 (--terraform-version)" in p.stdout
+    p = cli(["validate", "--frobnicate", str(mod)], trees)
+    assert p.returncode == 1 and "unknown option" in p.stderr
 
 
 def test_lint_lock_docs(trees):
