@@ -150,7 +150,8 @@ def check_tree(root: str, modules: Optional[list[str]] = None,
         os.chdir(root)
         # a module at ROOT itself ("." among the modules) already covers every sub-directory
         top = ["."] if "." in mods or not mods else sorted({m.split(os.sep)[0] for m in mods})
-        fmt = run_fmt(top, recursive=True, check=True, want_diff=True)
+        # diffs here feed the markdown report: made in-process, no `diff` program spawned
+        fmt = run_fmt(top, recursive=True, check=True, want_diff=True, external_diff=False)
     finally:
         os.chdir(cwd)
     reports = [check_module(root, rel, terraform_version)[0] for rel in mods]

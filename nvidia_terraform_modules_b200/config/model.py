@@ -463,7 +463,7 @@ class _Loader:
         attrs = b.body.attributes
         if "type" in attrs:
             try:
-                v.type = typeexpr.parse_type(attrs["type"].expr)
+                v.type = self.quoted_type(f, attrs["type"].expr) or typeexpr.parse_type(attrs["type"].expr)
             except typeexpr.TypeError_ as e:
                 self.diag(ERROR, "Invalid type specification", str(e), f.path, e.node, "type")
             self.optional_attributes(f, b, attrs["type"].expr)
@@ -488,6 +488,33 @@ class _Loader:
                           "A null default value is not valid when nullable=false.",
                           f.path, attrs["default"].expr, "type")
         self.m.variables[name] = v
+
+    def quoted_type(self, f: SourceFile, expr: A.Expr) -> Optional[typeexpr.Type]:
+        """``type = "string"`` / ``"list"`` / ``"map"``: the 0.11 spelling.  0.12-0.14 read it
+        with a deprecation warning, 0.15 turned it into an error (``fmt`` rewrites it either
+        way: fmt/rewrites.py).  Returns the type when the old spelling was understood."""
+        word = expr.literal_value() if isinstance(expr, A.Template) and not expr.heredoc else None
+        if word is None:
+            return None
+        better = {"string": "", "list": " and write list(string) instead to explicitly indicate that the list "
+                  "elements are strings", "map": " and write map(string) instead to explicitly indicate that the "
+                  "map elements are strings"}
+        if word not in better:
+            self.diag(ERROR, "Invalid legacy variable type hint",
+                      "To provide a full type expression, remove the surrounding quotes and give the type "
+                      "expression directly.", f.path, expr, "type")
+            return typeexpr.Type("any")
+        if self.v.release >= tfversion.LEGACY_FUNCTIONS_REMOVED:        # the same clean-up release, 0.15
+            self.diag(ERROR, "Invalid quoted type constraints",
+                      "Terraform 0.11 and earlier required type constraints to be given in quotes, but that form "
+                      "is now deprecated and will be removed in a future version of Terraform. Remove the quotes "
+                      f"around \"{word}\"{better[word]}.", f.path, expr, "type")
+        else:
+            self.diag(WARNING, "Quoted type constraints are deprecated",
+                      "Terraform 0.11 and earlier required type constraints to be given in quotes, but that form "
+                      "is now deprecated and will be removed in a future version of Terraform. To silence this "
+                      f"warning, remove the quotes around \"{word}\"{better[word]}.", f.path, expr, "deprecated")
+        return typeexpr.Type(word) if word == "string" else typeexpr.Type(word, elem=typeexpr.Type("string"))
 
     def block_locals(self, f: SourceFile, b: A.Block) -> None:
         for item in b.body.items:
@@ -588,9 +615,10 @@ class _Loader:
                               f.path, attrs["version"].expr, "version")
                 if mc.source is not None and not mc.is_registry:
                     self.diag(ERROR, "Invalid registry module source address",
-                              f"Cannot apply a version constraint to module \"{name}\" because its source "
-                              f"\"{mc.source}\" is not a module registry address.",
-                              f.path, attrs["version"], "version")
+                              f"Failed to parse module registry address: \"{mc.source}\" is not a module registry "
+                              "address.\n\nTerraform assumed that you intended a module registry source address "
+                              "because you also set the argument \"version\", which applies only to registry modules.",
+                              f.path, attrs["source"].expr, "version")
         for blk in b.body.blocks:
             if blk.type in ("lifecycle", "locals", "provider", "dynamic"):
                 self.diag(ERROR, "Reserved block type name in module block" if blk.type != "dynamic"
@@ -660,9 +688,9 @@ class _Loader:
                 ic = blk.body.attributes.get("ignore_changes")
                 if ic is not None and not isinstance(ic.expr, A.TupleCons) and not (
                         isinstance(ic.expr, A.ScopeTraversal) and ic.expr.root == "all" and not ic.expr.steps):
-                    self.diag(ERROR, "Invalid ignore_changes ruleset",
-                              "The ignore_changes argument must be either a list of attribute names or the "
-                              "special keyword \"all\".", f.path, ic.expr, "structure")
+                    # neither the keyword ``all`` nor a list: Terraform asks HCL for a static list
+                    self.diag(ERROR, "Invalid expression", "A static list expression is required.",
+                              f.path, ic.expr, "structure")
             elif blk.type in ("provisioner", "connection") and mode != "managed":
                 self.diag(ERROR, "Unsupported block type" if blk.type == "connection" or mode == "ephemeral"
                           else "Data resources do not have provisioners",
@@ -700,10 +728,13 @@ class _Loader:
                 self.diag(ERROR, "Unsupported argument",
                           f"An argument named \"{a}\" is not expected here.", f.path, attrs[a], "structure")
         content = blk.body.blocks_of("content")
-        if len(content) != 1:
-            self.diag(ERROR, "Insufficient content blocks" if not content else "Too many content blocks",
-                      "At least 1 \"content\" blocks are required." if not content else
-                      "No more than 1 \"content\" blocks are allowed", f.path, blk, "structure")
+        if not content:
+            self.diag(ERROR, "Missing dynamic content block",
+                      "A dynamic block must have a nested block of type \"content\" to describe the body of each "
+                      "generated block.", f.path, blk, "structure")
+        elif len(content) > 1:
+            self.diag(ERROR, "Multiple content blocks",
+                      "Only one nested content block is allowed for each dynamic block.", f.path, content[1], "structure")
         for other in blk.body.blocks:
             if other.type != "content":
                 self.diag(ERROR, "Unsupported block type",

@@ -349,7 +349,7 @@ class Validator:
                 if isinstance(it.expr, A.ScopeTraversal) and not it.expr.steps:
                     iterator = it.expr.root
                 else:
-                    self.diag(ERROR, "Invalid expression", "Dynamic iterator must be a single variable name.",
+                    self.diag(ERROR, "Invalid dynamic iterator name", "Dynamic iterator must be a single variable name.",
                               ctx, it.expr, "structure")
             if "for_each" in attrs:
                 self.attr_value(attrs["for_each"], ctx)

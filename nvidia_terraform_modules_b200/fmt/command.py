@@ -21,9 +21,12 @@ from __future__ import annotations
 
 import difflib
 import os
+import shutil
+import subprocess
 import sys
+import tempfile
 from dataclasses import dataclass, field
-from typing import Iterable, TextIO
+from typing import Iterable, Optional, TextIO
 
 from ..hcl.diagnostics import Diagnostic, has_errors
 from ..hcl.parser import parse, parse_path
@@ -91,7 +94,48 @@ class FmtResult:
         return 0
 
 
-def unified_diff(path: str, old: str, new: str) -> str:
+_DIFF_PROGRAM = shutil.which("diff")
+
+
+def _external_diff(path: str, old: str, new: str) -> Optional[str]:
+    with tempfile.TemporaryDirectory(prefix="tffmt_") as d:
+        files = []
+        for name, text in (("old", old), ("new", new)):
+            files.append(os.path.join(d, name))
+            with open(files[-1], "w", encoding="utf-8", newline="") as fh:
+                fh.write(text)
+        try:
+            p = subprocess.run([_DIFF_PROGRAM, f"--label=old/{path}", f"--label=new/{path}", "-u", *files],
+                               capture_output=True, timeout=60)
+        except (OSError, subprocess.SubprocessError):
+            return None
+    if p.returncode not in (0, 1):          # 1 = "files differ"
+        return None
+    return p.stdout.decode("utf-8", errors="replace")
+
+
+def _hunk_range(start: int, stop: int) -> str:
+    """``start,count`` the way ``diff -u`` writes it: the count is left out when it is
+    1, and an empty range names the line before it."""
+    count = stop - start
+    if count == 1:
+        return str(start + 1)
+    if count == 0:
+        return f"{start},0"
+    return f"{start + 1},{count}"
+
+
+def unified_diff(path: str, old: str, new: str, external: bool = True) -> str:
+    """What ``terraform fmt -diff`` prints.  Terraform shells out to
+    ``diff --label=old/PATH --label=new/PATH -u``; so does this when a ``diff`` program
+    is installed (byte-identical output by construction).  Without one -- Terraform
+    itself fails there -- the same GNU unified format is produced in-process; the two
+    agree whenever the changed lines are not repeated elsewhere in the file, which is
+    the case ``diff`` and ``difflib`` may pair up differently."""
+    if external and _DIFF_PROGRAM:
+        text = _external_diff(path, old, new)
+        if text is not None:
+            return text
     a = old.splitlines(keepends=True)
     b = new.splitlines(keepends=True)
     out = [f"--- old/{path}\n", f"+++ new/{path}\n"]
@@ -103,7 +147,7 @@ def unified_diff(path: str, old: str, new: str) -> str:
     matcher = difflib.SequenceMatcher(None, a, b, autojunk=False)
     for group in matcher.get_grouped_opcodes(3):
         a0, a1, b0, b1 = group[0][1], group[-1][2], group[0][3], group[-1][4]
-        out.append(f"@@ -{a0 + 1},{a1 - a0} +{b0 + 1},{b1 - b0} @@\n")
+        out.append(f"@@ -{_hunk_range(a0, a1)} +{_hunk_range(b0, b1)} @@\n")
         for tag, i1, i2, j1, j2 in group:
             if tag == "equal":
                 for ln in a[i1:i2]:
@@ -123,7 +167,7 @@ def _display(path: str) -> str:
 
 
 def run_fmt(targets: Iterable[str], *, recursive: bool = False, write: bool = True,
-            want_diff: bool = False, check: bool = False) -> FmtResult:
+            want_diff: bool = False, check: bool = False, external_diff: bool = True) -> FmtResult:
     res = FmtResult()
     if check:
         write = False
@@ -155,7 +199,7 @@ def run_fmt(targets: Iterable[str], *, recursive: bool = False, write: bool = Tr
             continue
         res.changed.append(_display(path))
         if want_diff:
-            res.diffs[_display(path)] = unified_diff(_display(path), src, out)
+            res.diffs[_display(path)] = unified_diff(_display(path), src, out, external_diff)
         if write:
             with open(path, "w", encoding="utf-8", newline="") as fh:
                 fh.write(out)

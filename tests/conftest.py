@@ -21,6 +21,8 @@ REFERENCE = os.environ.get("TF_REFERENCE_ROOT", "/root/reference")
 def pytest_configure(config):
     config.addinivalue_line("markers", "gpu: needs a CUDA device (none exist in this repo; see DESIGN.md)")
     config.addinivalue_line("markers", "reference: reads /root/reference (skipped where it is absent)")
+    config.addinivalue_line("markers", "terraform: runs the real terraform / terraform-docs binaries beside the "
+                                       "stand-ins (skipped until $TF_BIN or PATH supplies them)")
     config.addinivalue_line("filterwarnings", "ignore:Generating overly large repr")
 
 

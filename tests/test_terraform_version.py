@@ -236,6 +236,15 @@ def test_list_and_map_functions_were_only_deprecated_before_0_15(module_dir):
     assert errors(new) == [("Error in function call", 2)]
 
 
+def test_quoted_type_keywords_were_only_deprecated_before_0_15(module_dir):
+    text = 'variable "a" {\n  type = "list"\n}\n'
+    old = run(module_dir, text, "0.14")
+    assert errors(old) == [] and [(d.severity, d.summary) for d in old.diags] == [
+        (WARNING, "Quoted type constraints are deprecated")]
+    assert str(old.module.variables["a"].type) == "list(string)"
+    assert errors(run(module_dir, text, "0.15")) == [("Invalid quoted type constraints", 2)]
+
+
 def test_every_gated_function_is_a_known_function():
     from nvidia_terraform_modules_b200.config.functions import FUNCTIONS
     assert set(tfversion.FUNCTION_SINCE) <= set(FUNCTIONS)

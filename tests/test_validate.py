@@ -241,7 +241,8 @@ def test_deprecation_warnings_do_not_make_a_module_invalid(module_dir):
     ('variable "count" {}\n', "Invalid variable name"),
     ('variable "a" {\n  typ = string\n}\n', "Unsupported argument"),
     ('variable "a" {\n  type = strng\n}\n', "Invalid type specification"),
-    ('variable "a" {\n  type = "string"\n}\n', "Invalid type specification"),
+    ('variable "a" {\n  type = "string"\n}\n', "Invalid quoted type constraints"),
+    ('variable "a" {\n  type = "list(string)"\n}\n', "Invalid legacy variable type hint"),
     ('variable "a" {\n  type    = number\n  default = "x"\n}\n', "Invalid default value for variable"),
     ('variable "a" {\n  type    = string\n  default = var.b\n}\n', "Variables not allowed"),
     ('variable "a" {\n  default  = null\n  nullable = false\n}\n', "Invalid default value for variable"),
@@ -259,7 +260,7 @@ def test_deprecation_warnings_do_not_make_a_module_invalid(module_dir):
     ('resource "a_b" "c" {\n  lifecycle {\n    frob = 1\n  }\n}\n', "Unsupported argument"),
     ('data "a_b" "c" {\n  provisioner "x" {}\n}\n', "Data resources do not have provisioners"),
     ('resource "a_b" "c" {\n  dynamic "x" {\n    content {}\n  }\n}\n', "Missing required argument"),
-    ('resource "a_b" "c" {\n  dynamic "x" {\n    for_each = []\n  }\n}\n', "Insufficient content blocks"),
+    ('resource "a_b" "c" {\n  dynamic "x" {\n    for_each = []\n  }\n}\n', "Missing dynamic content block"),
     ('provider "aws" {}\nprovider "aws" {}\n', "Duplicate provider configuration"),
     ('provider "aws" {\n  alias = "9x"\n}\n', "Invalid provider configuration alias"),
     ('terraform {\n  required_version = ">> 1"\n}\n', "Invalid version constraint"),
@@ -315,7 +316,7 @@ data "aws_d" "z" {
      "Invalid variable validation condition"),
     ('variable "a" {\n  validation {\n    condition = var.a != ""\n  }\n}\n', "Missing required argument"),
     ('output "o" {\n  value = 1\n  precondition {\n    error_message = "m"\n  }\n}\n', "Missing required argument"),
-    ('resource "a_b" "c" {\n  lifecycle {\n    ignore_changes = "tags"\n  }\n}\n', "Invalid ignore_changes ruleset"),
+    ('resource "a_b" "c" {\n  lifecycle {\n    ignore_changes = "tags"\n  }\n}\n', "Invalid expression"),
     ('resource "a_b" "c" {\n  lifecycle {\n    ignore_changes = all\n  }\n}\n', None),
     ('resource "a_b" "c" {\n  lifecycle {\n    postcondition {\n      condition = self.id != ""\n'
      '      error_message = "m"\n    }\n  }\n}\n', None),
