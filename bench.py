@@ -58,6 +58,14 @@ def parse_args() -> argparse.Namespace:
     return ap.parse_args()
 
 
+def identities(report: dict) -> list[list[str]]:
+    """``[kind, file]`` of everything a ``check`` report found, sorted: the same
+    comparison ``__graft_entry__.smoke()`` makes against the planted defects."""
+    out = [[d["rule"], d["file"]] for m in report["modules"] for d in m["diagnostics"]]
+    out += [["fmt", f] for f in report["fmt"]["changed"]]
+    return sorted(out)
+
+
 def main() -> int:
     args = parse_args()
     rank = int(os.environ.get("RANK", "0"))
@@ -100,11 +108,14 @@ def main() -> int:
         for _ in range(args.e2e_steps):
             proc = subprocess.run(cmd, env=env, capture_output=True, text=True, check=False)
         e2e_dt = (time.perf_counter() - t0) / args.e2e_steps
-        cli_counts = json.loads(proc.stdout)["counts"]
-
-        counts = rep.to_dict()["counts"]
-        planted = len(tree.planted)
-        found = counts["error"] + counts["warning"] + counts["notice"] + counts["fmt_differing"]
+        # WHICH defects were found, not how many: a missed defect plus a false positive
+        # must not cancel out (in-process leg and CLI leg alike)
+        planted = sorted([p.kind, p.file] for p in tree.planted)
+        found = identities(rep.to_dict())
+        cli_found = identities(json.loads(proc.stdout))
+        mismatch = {leg: {"missed": [x for x in planted if x not in got],
+                          "unexpected": [x for x in got if x not in planted]}
+                    for leg, got in (("in_process", found), ("cli", cli_found)) if got != planted}
         line = {
             "metric": "static_check_throughput (CPU stand-in; BASELINE.json metric is: " + BASELINE_METRIC + ")",
             "value": round(value, 3),
@@ -121,9 +132,10 @@ def main() -> int:
             "data": "synthetic",
             "config": {"workload": f"fmt+validate+lint+lock+docs over {len(tree.modules)} synthetic modules, "
                                    f"{len(rep.fmt.checked)} formattable files, {rep.bytes_scanned} bytes, "
-                                   f"{planted} planted defects (seed {args.seed}); inputs far smaller than any cache",
+                                   f"{len(planted)} planted defects (seed {args.seed}); inputs far smaller than any cache",
                        "status": STAND_IN},
-            "findings": {"planted": planted, "found": found, "cli_found": cli_counts},
+            "findings": {"planted": len(planted), "found": len(found), "cli_found": len(cli_found),
+                         "identical_to_planted": not mismatch, "mismatch": mismatch or None},
             "gpu_launches": 0,
             "roofline": None,
             "roofline_note": NO_GPU,
@@ -134,7 +146,7 @@ def main() -> int:
                     "ms_per_step": round(e2e_dt * 1e3, 1), "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
         }
         print(json.dumps(line))
-        return 0 if found == planted else 1
+        return 1 if mismatch else 0
     finally:
         shutil.rmtree(workdir, ignore_errors=True)
 

@@ -67,6 +67,8 @@ def render_markdown(rep: TreeReport, title: str = "Static-check findings") -> st
                    f"{by_sev.get(NOTICE, 0)} notices")
         out.append("")
         out.append("Declares " + ", ".join(f"{v} {k.replace('_', ' ')}" for k, v in m.counts.items()) + ".")
+        if m.terraform_version_source:
+            out.append(f"Validated as {m.terraform_version_source}.")
         out.append("")
         major = [d for d in diags if d.severity in (ERROR, WARNING)]
         if major:

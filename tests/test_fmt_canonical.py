@@ -4,7 +4,7 @@ The expected texts were written by hand from Terraform's documented style
 conventions ("Style Conventions": two-space indent, aligned equals signs for
 consecutive single-line arguments, ...) and from how files in the wild look
 after ``terraform fmt`` -- NOT by running the code under test.  Parity with the
-real binary is unpinned (none is available offline); tests/test_reference_golden.py
+real binary is unpinned (none is available offline); tests/test_reference_evidence.py
 adds the evidence the reference tree itself provides.
 """
 import pytest

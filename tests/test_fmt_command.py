@@ -97,3 +97,30 @@ def test_result_counts_bytes(tree):
     res = run_fmt(["mod"], recursive=True, check=True)
     assert res.bytes_checked == sum(os.path.getsize(p) for p in
                                     ["mod/examples/x/main.tf", "mod/main.tf", "mod/ok.tf", "mod/terraform.tfvars"])
+
+
+def test_in_process_diff_equals_the_diff_program_on_white_space_edits():
+    """`terraform fmt -diff` shells out to `diff -u`; the fallback used where no such program
+    exists must print the same bytes -- hunk ranges (`-3`, `-2,0`), context, and the
+    "\\ No newline at end of file" marker included."""
+    import random
+    from nvidia_terraform_modules_b200.fmt import command
+    if not command._DIFF_PROGRAM:
+        pytest.skip("no diff program on this machine")
+    rng = random.Random(5)
+    compared = 0
+    for _ in range(150):
+        n = rng.randint(1, 30)
+        old = [f"name{i} = {rng.randint(0, 99)}\n" for i in range(n)]
+        new = list(old)
+        for _ in range(rng.randint(1, 4)):
+            i = rng.randrange(n)
+            new[i] = new[i].replace(" = ", " " * rng.randint(2, 5) + "= ")
+        if rng.random() < 0.3:
+            old[-1], new[-1] = old[-1].rstrip("\n"), new[-1].rstrip("\n")
+        a, b = "".join(old), "".join(new)
+        if a == b:
+            continue
+        compared += 1
+        assert command.unified_diff("x.tf", a, b, external=False) == command.unified_diff("x.tf", a, b, external=True)
+    assert compared > 100

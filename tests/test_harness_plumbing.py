@@ -19,7 +19,7 @@ ROOT = os.path.dirname(HERE)
 
 def _run_harness(version: str, *extra: str) -> subprocess.CompletedProcess:
     env = dict(os.environ, TF_BIN=os.path.join(HERE, "support", "fake_terraform.py"),
-               FAKE_TERRAFORM_VERSION=version, PYTHONPATH=ROOT)
+               FAKE_TERRAFORM_VERSION=version, PYTHONPATH=ROOT, TF_HARNESS_FMT_SAMPLE="60")
     env.pop("TF_PLUGIN_MIRROR", None)
     env["TFDOCS_BIN"] = os.path.join(HERE, "support", "fake_terraform_docs.py")
     return subprocess.run([sys.executable, "-m", "pytest", os.path.join(HERE, "test_against_terraform.py"),
