@@ -243,6 +243,10 @@ def main(argv: list[str], stdout: TextIO = sys.stdout, stderr: TextIO = sys.stde
                   want_diff=opts["diff"], check=opts["check"])
     for d in res.diags:
         stderr.write(d.format() + "\n\n")
+    if has_errors(res.diags) and opts["check"]:
+        # Terraform buffers -check output and gives up before printing it when any
+        # file failed to parse; without -check the names stream out as files are done
+        return 2
     for path in res.changed:
         if opts["list"]:
             stdout.write(path + "\n")

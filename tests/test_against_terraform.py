@@ -373,6 +373,11 @@ MIRROR_CASES: dict[str, dict[str, str]] = {
 }
 
 
+# `terraform init` refuses a configuration that does not load, so the child module of such
+# a case is never installed and validate adds this on top of the error under test
+INIT_ARTEFACTS = {"Module not installed"}
+
+
 def _write(root: str, files: dict[str, str]) -> None:
     for rel, text in files.items():
         path = os.path.join(root, rel)
@@ -390,6 +395,8 @@ def _real_validate(root: str, plugin_dir: str | None = None) -> list[tuple]:
     data = json.loads(p.stdout)
     out = []
     for d in data["diagnostics"]:
+        if d["summary"] in INIT_ARTEFACTS:
+            continue
         rng = d.get("range") or {}
         out.append((d["severity"], d["summary"], rng.get("filename", ""), (rng.get("start") or {}).get("line", 0)))
     return sorted(_normal(d) for d in out)

@@ -11,7 +11,11 @@ from nvidia_terraform_modules_b200.hcl.parser import parse  # noqa: E402
 from nvidia_terraform_modules_b200.hcl.scanner import scan  # noqa: E402
 from nvidia_terraform_modules_b200.hcl.tokens import T, render  # noqa: E402
 
-COMMON = settings(max_examples=300, deadline=None, suppress_health_check=[HealthCheck.too_slow])
+import os  # noqa: E402
+
+# FUZZ_EXAMPLES=5000 python -m pytest tests/test_fuzz_properties.py   for a long run
+COMMON = settings(max_examples=int(os.environ.get("FUZZ_EXAMPLES", "300")), deadline=None,
+                  suppress_health_check=[HealthCheck.too_slow, HealthCheck.function_scoped_fixture])
 
 # text biased towards characters that mean something to the scanner
 ALPHABET = st.sampled_from(list("abxyz_-019 \t\n\r\"'\\${}%[](),.=<>!&|?:*/+#~") + ["${", "%{", "<<EOT\n", "EOT\n", "/*",
@@ -126,3 +130,74 @@ def test_fmt_output_obeys_the_visible_rules(src):
         indent = len(line) - len(line.lstrip(" "))
         if line.strip() and not line.lstrip().startswith(("*", "/*")):
             assert indent % 2 == 0, repr(line)
+
+
+# ------------------------------------------- layout independence, validate robustness
+@COMMON
+@given(PROGRAM, st.integers(0, 10 ** 6))
+def test_fmt_answer_does_not_depend_on_the_layout_it_starts_from(src, seed):
+    """Format, destroy the white space two ways (tests/scramble.py), format again: the
+    same text must come back.  The generated-program form of the recovery test that
+    tests/test_reference_evidence.py runs on the reference's own files."""
+    import random
+    from scramble import damage_lines, damage_tokens
+    want, diags = format_source(src, "gen.tf")
+    assert not diags
+    for fn in (damage_lines, damage_tokens):
+        bad = fn(want, random.Random(seed))
+        assert signature(bad) == signature(want)
+        got, diags = format_source(bad, "gen.tf")
+        assert not diags and got == want, (fn.__name__, bad)
+
+
+RELEASES = st.sampled_from(["0.13", "0.14", "0.15", "1.0", "1.2", "1.3", "1.5", "1.8", "1.9", "1.10"])
+TOP_LEVEL = st.sampled_from(['variable "v" ', 'output "o" ', "locals ", 'resource "a_b" "c" ', 'data "a_b" "c" ',
+                             'module "m" ', "terraform ", 'provider "p" ', "moved ", "import ", 'check "k" ',
+                             "removed ", 'ephemeral "a_b" "e" ', 'variable "w" ', 'resource "a_b" "d" '])
+INNER_NAME = st.sampled_from(["type", "default", "value", "count", "for_each", "source", "depends_on", "condition",
+                              "error_message", "sensitive", "nullable", "from", "to", "id", "provider", "version",
+                              "required_version", "experiments", "description", "x", "when", "on_failure", "iterator",
+                              "labels", "ignore_changes", "ephemeral", "validation", "lifecycle"])
+INNER_BLOCK = st.sampled_from(["validation", "lifecycle", "precondition", "postcondition", "provisioner \"p\"",
+                               "connection", "dynamic \"d\"", "content", "assert", "backend \"b\"",
+                               "required_providers", "data \"a_b\" \"n\"", "cloud", "nested"])
+
+
+def module_bodies(depth=2):
+    attr = st.tuples(INNER_NAME, exprs()).map(lambda t: f"  {t[0]} = {t[1]}\n")
+    items = [attr, attr]
+    if depth:
+        items.append(st.tuples(INNER_BLOCK, module_bodies(depth - 1)).map(lambda t: f"  {t[0]} {{\n{t[1]}  }}\n"))
+    return st.lists(st.one_of(*items), max_size=5).map("".join)
+
+
+MODULE = st.lists(st.tuples(TOP_LEVEL, module_bodies()).map(lambda t: f"{t[0]}{{\n{t[1]}}}\n"), max_size=6).map("".join)
+
+
+@COMMON
+@given(MODULE, RELEASES)
+def test_validate_reports_instead_of_raising(tmp_path_factory, src, release):
+    """Structurally plausible nonsense under every restated release: diagnostics, never a
+    traceback, and every diagnostic carries a summary, a file and a line."""
+    from nvidia_terraform_modules_b200.check import clear_caches
+    from nvidia_terraform_modules_b200.config.validate import validate_module
+    from nvidia_terraform_modules_b200.lint.rules import run_rules
+    d = tmp_path_factory.mktemp("fz")
+    (d / "main.tf").write_text(src)
+    clear_caches()
+    res = validate_module(str(d), str(d), release)
+    assert res.module.restated.text == release
+    for diag in res.diags:
+        assert diag.summary and diag.file == "main.tf" and diag.line >= 0
+    run_rules(res)            # the lint rules walk the same tree: they must not raise either
+
+
+@COMMON
+@given(NOISE, RELEASES)
+def test_validate_survives_noise(tmp_path_factory, src, release):
+    from nvidia_terraform_modules_b200.check import clear_caches
+    from nvidia_terraform_modules_b200.config.validate import validate_module
+    d = tmp_path_factory.mktemp("fn")
+    (d / "main.tf").write_text(src, encoding="utf-8", newline="")
+    clear_caches()
+    validate_module(str(d), str(d), release)
