@@ -171,6 +171,20 @@ def module_bodies(depth=2):
     return st.lists(st.one_of(*items), max_size=5).map("".join)
 
 
+_DIRS: dict = {}
+
+
+def _one_dir(factory, name):
+    """One directory per property, rewritten for every example (thousands of examples
+    must not leave thousands of directories behind)."""
+    if name not in _DIRS:
+        _DIRS[name] = factory.mktemp(name)
+    target = _DIRS[name] / "main.tf"
+    if target.exists():
+        target.unlink()          # (truncating in place is very slow on some container file systems)
+    return _DIRS[name]
+
+
 MODULE = st.lists(st.tuples(TOP_LEVEL, module_bodies()).map(lambda t: f"{t[0]}{{\n{t[1]}}}\n"), max_size=6).map("".join)
 
 
@@ -182,7 +196,7 @@ def test_validate_reports_instead_of_raising(tmp_path_factory, src, release):
     from nvidia_terraform_modules_b200.check import clear_caches
     from nvidia_terraform_modules_b200.config.validate import validate_module
     from nvidia_terraform_modules_b200.lint.rules import run_rules
-    d = tmp_path_factory.mktemp("fz")
+    d = _one_dir(tmp_path_factory, "fz")
     (d / "main.tf").write_text(src)
     clear_caches()
     res = validate_module(str(d), str(d), release)
@@ -197,7 +211,7 @@ def test_validate_reports_instead_of_raising(tmp_path_factory, src, release):
 def test_validate_survives_noise(tmp_path_factory, src, release):
     from nvidia_terraform_modules_b200.check import clear_caches
     from nvidia_terraform_modules_b200.config.validate import validate_module
-    d = tmp_path_factory.mktemp("fn")
+    d = _one_dir(tmp_path_factory, "fn")
     (d / "main.tf").write_text(src, encoding="utf-8", newline="")
     clear_caches()
     validate_module(str(d), str(d), release)
