@@ -881,8 +881,16 @@ class _Loader:
             if isinstance(val, str):
                 req.constraint_text = val              # legacy: aws = "~> 4.0"
             elif isinstance(val, dict):
+                aliases_known = self.v.has("required_providers:configuration_aliases")
                 for k in val:
-                    if k not in ("source", "version", "configuration_aliases"):
+                    if k == "configuration_aliases" and not aliases_known:
+                        self.diag(ERROR, "Invalid required_providers object",
+                                  "required_providers objects can only contain \"version\" and \"source\" "
+                                  "attributes. To configure a provider, use a \"provider\" block."
+                                  + self.needs("required_providers:configuration_aliases",
+                                               "The \"configuration_aliases\" attribute"),
+                                  f.path, item.expr, "terraform-version")
+                    elif k not in ("source", "version", "configuration_aliases"):
                         self.diag(ERROR, "Invalid required_providers object",
                                   "required_providers objects can only contain \"version\", \"source\" and "
                                   "\"configuration_aliases\" attributes. To configure a provider, use a "

@@ -58,6 +58,7 @@ SINCE: dict[str, Release] = {
     "lifecycle:postcondition": (1, 2),
     "lifecycle:replace_triggered_by": (1, 2),
     "terraform:cloud": (1, 1),
+    "required_providers:configuration_aliases": (0, 15),
     "import:for_each": (1, 7),
     "removed:provisioner": (1, 9),
     # language behaviour

@@ -205,6 +205,15 @@ def test_provider_defined_functions_gate(module_dir):
     assert errors(run(module_dir, core, "1.8")) == []
 
 
+def test_configuration_aliases_gate(module_dir):
+    text = ('terraform {\n  required_providers {\n    aws = {\n      source                = "hashicorp/aws"\n'
+            '      configuration_aliases = [aws.west]\n    }\n  }\n}\n')
+    old = run(module_dir, text, "0.14")
+    assert errors(old) == [("Invalid required_providers object", 3)]
+    assert "needs Terraform 0.15 or later" in old.diags[0].detail
+    assert errors(run(module_dir, text, "0.15")) == []
+
+
 def test_terraform_applying_gate(module_dir):
     text = 'output "o" {\n  value = terraform.applying\n}\n'
     assert errors(run(module_dir, text, "1.9")) == [('Invalid "terraform" attribute', 2)]
