@@ -204,6 +204,10 @@ def test_validate_reports_instead_of_raising(tmp_path_factory, src, release):
     for diag in res.diags:
         assert diag.summary and diag.file == "main.tf" and diag.line >= 0
     run_rules(res)            # the lint rules walk the same tree: they must not raise either
+    from nvidia_terraform_modules_b200.docs.tfdocs import inject, parse_readme, render
+    tables = render(res.module)
+    assert inject(inject("# T\n", tables), tables) == inject("# T\n", tables)
+    assert set(parse_readme(tables)) <= {"Requirements", "Providers", "Modules", "Resources", "Inputs", "Outputs"}
 
 
 @COMMON
