@@ -420,6 +420,24 @@ def check_readme(m: Module, readme_path: str, display: Optional[str] = None) -> 
                     f"\"{r.type}.{r.name}\" is not documented in the README",
                     f"Declared at {r.file}:{r.line}.", "docs-missing-resource")
 
+    # ---- Providers (names only: the version column depends on whether a lock file
+    # existed when the table was generated, "n/a" otherwise)
+    t = tables.get("Providers")
+    if t is not None:
+        used = m.used_provider_names()
+        seen = set()
+        for line, cells in t.rows:
+            name = _cell_name(cells[0])
+            seen.add(name)
+            if name not in used:
+                add(line, f"README lists provider \"{name}\" which no resource or data source uses", "",
+                    "docs-unknown-provider")
+        for name in sorted(used):
+            if name not in seen:
+                first = min(used[name], key=lambda r: (r.file, r.line))
+                add(t.heading_line, f"provider \"{name}\" is not documented in the README",
+                    f"Used by {first.addr} at {first.file}:{first.line}.", "docs-missing-provider")
+
     # ---- Requirements
     t = tables.get("Requirements")
     if t is not None:

@@ -166,3 +166,22 @@ def test_inject_refuses_when_generated_sections_are_split_by_prose(module_dir):
     loose = fresh[:cut] + "a stray paragraph\n\n" + fresh[cut:]
     with pytest.raises(InjectRefused):
         inject(loose, fresh)
+
+
+def test_providers_table_is_checked_by_name(module_dir, tmp_path):
+    _, m = module(module_dir)
+    fresh = render(m)
+    readme = tmp_path / "P.md"
+    start = fresh.index("## Providers")
+    end = fresh.index("## Modules")
+    rows = [ln for ln in fresh[start:end].splitlines() if ln.startswith("| <a")]
+    assert rows, "the fixture module uses at least one provider"
+    doctored = fresh[:start] + "## Providers\n\n| Name | Version |\n|------|---------|\n" \
+        "| <a name=\"provider_ghost\"></a> [ghost](#provider\\_ghost) | n/a |\n\n" + fresh[end:]
+    readme.write_text(doctored)
+    got = sorted((d.rule, d.summary) for d in check_readme(m, str(readme)))
+    assert ("docs-unknown-provider", 'README lists provider "ghost" which no resource or data source uses') in got
+    assert any(rule == "docs-missing-provider" for rule, _ in got)
+    # a version column of "n/a" (README generated before a lock file existed) is not drift
+    readme.write_text(fresh.replace(rows[0], rows[0].rsplit("|", 2)[0] + "| n/a |"))
+    assert check_readme(m, str(readme)) == []
