@@ -199,6 +199,22 @@ def test_fmt_write_leaves_the_same_bytes_on_disk(defect_tree, tmp_path):
             assert a.read() == b.read(), rel
 
 
+@pytest.mark.reference
+def test_fmt_check_recursive_on_the_reference_is_baseline_config_1():
+    """BASELINE.json config 1, verbatim: ``terraform fmt -check -recursive`` over eks/, aks/,
+    gke/.  -check never writes, so the read-only mount is safe.  SURVEY.md section 4 predicts
+    exit 3 and five files (tests/golden/survey_expectations.json)."""
+    if not os.path.isdir(os.path.join(REFERENCE, "eks")):
+        pytest.skip("reference tree not present on this machine")
+    args = ["-check", "-recursive", "eks", "aks", "gke"]
+    real = tf(["fmt", "-no-color", *args], REFERENCE)
+    code, out, _ = ours_fmt(args, REFERENCE)
+    assert (real.returncode, real.stdout) == (code, out), explain(real.stdout, out, "stdout")
+    with open(os.path.join(os.path.dirname(__file__), "golden", "survey_expectations.json")) as fh:
+        predicted = json.load(fh)["fmt_files_predicted_to_differ"]["files"]
+    assert real.returncode == 3 and sorted(real.stdout.split()) == predicted
+
+
 def test_fmt_syntax_error_exit_code(tmp_path):
     (tmp_path / "broken.tf").write_text("a = (\n")
     (tmp_path / "fine.tf").write_text("a   = 1\n")
