@@ -116,6 +116,15 @@ def test_readme_rows_reproduce_real_terraform_docs_output(survey, measured):
     assert (total, same) == (226, 219)
 
 
+def test_version_constraints_are_respelt_the_way_terraform_init_records_them(measured):
+    """eks/versions.tf writes "~>4.45.0"; `terraform init` recorded "~> 4.45.0" in
+    eks/.terraform.lock.hcl.  All eight constrained providers across the six modules agree."""
+    rec = measured["lock_constraints"]
+    assert sum(r["required_providers_with_a_constraint"] for r in rec.values()) == 8
+    for module, r in rec.items():
+        assert r["canonical_spelling_found_in_lock_file"] == r["required_providers_with_a_constraint"], module
+
+
 def test_the_files_the_authors_left_canonical_are_fixed_points(measured):
     assert measured["fmt_fixed_points"] == {"files_left_canonical_by_the_authors": 33, "unchanged_by_fmt": 33}
 
