@@ -440,7 +440,14 @@ class Validator:
                     self.expr(p, ctx)
         elif isinstance(e, A.ObjectKey):
             if e.bare_name is None:
-                self.expr(e.wrapped, ctx)
+                w = e.wrapped
+                if isinstance(w, A.ScopeTraversal) and w.steps and not e.forced_expr:
+                    self.diag(ERROR, "Ambiguous attribute key",
+                              "If this expression is intended to be a reference, wrap it in parentheses. If it's "
+                              "instead intended as a literal name containing periods, wrap it in quotes to create "
+                              "a string literal.", ctx, w, "syntax")
+                else:
+                    self.expr(w, ctx)
         else:
             if isinstance(e, A.Conditional):
                 clash = kinds.conditional_mismatch(e)

@@ -621,14 +621,12 @@ class Parser:
             key = self.parse_expr()
             bare = None
             if isinstance(key, A.ScopeTraversal):
+                # A dotted key (``aws.west = aws.usw2`` in a module's ``providers`` map) is
+                # accepted here: HCL objects to it only when the key is EVALUATED, so that
+                # callers reading the map statically may allow it.  config/validate.py
+                # raises "Ambiguous attribute key" wherever the object is a value.
                 if not key.steps:
                     bare = key.root
-                else:
-                    raise ParseError(Diagnostic(
-                        ERROR, "Ambiguous attribute key",
-                        "If this expression is intended to be a reference, wrap it in parentheses. "
-                        "If it's instead intended as a literal name containing periods, wrap it in quotes "
-                        "to create a string literal.", self.filename, key.pos.line, key.pos.col, "syntax"))
             elif isinstance(key, A.Literal) and key.text in ("true", "false", "null"):
                 bare = key.text
             okey = self._finish(A.ObjectKey(key, bare, forced), kmark)

@@ -117,8 +117,16 @@ def test_tuple_and_object_constructors():
     assert o.get("a").value == 1 and o.get("zz") is None
 
 
-def test_object_key_traversal_is_ambiguous():
-    assert errors("x = { a.b = 1 }\n") == [("Ambiguous attribute key", 1, 7)]
+def test_dotted_object_key_parses_and_is_judged_only_when_evaluated():
+    """HCL raises "Ambiguous attribute key" at evaluation time, precisely so that a static
+    reader -- Terraform's ``providers = { aws.west = aws.usw2 }`` -- may accept it.  The
+    parser therefore takes it; config/validate.py objects where the object is a value."""
+    assert errors("x = { a.b = 1 }\n") == []
+    o = expr("{ aws.west = aws.usw2 }")
+    key, value = o.items[0]
+    assert key.bare_name is None and key.literal_key() is None
+    assert isinstance(key.wrapped, A.ScopeTraversal) and key.wrapped.dotted() == "aws.west"
+    assert value.dotted() == "aws.usw2"
 
 
 def test_for_expressions():

@@ -387,3 +387,24 @@ def test_tfvars_are_checked_against_declarations(module_dir):
     res, diags = diag_set(module_dir, files)
     assert sorted(s for _, s in diags) == ["Invalid value for input variable", "Unexpected block",
                                            "Value for undeclared variable", "Variables not allowed"]
+
+
+def test_module_providers_map_takes_dotted_keys(module_dir):
+    """`providers = { aws.src = aws.a }` is the documented way to hand aliased provider
+    configurations to a child; it used to be rejected as a syntax error (and fmt refused
+    the file)."""
+    from nvidia_terraform_modules_b200.fmt.command import format_source
+    child = ('terraform {\n  required_providers {\n    aws = {\n      source                = "hashicorp/aws"\n'
+             '      configuration_aliases = [aws.src, aws.dst]\n    }\n  }\n}\n')
+    root = ('provider "aws" {\n  alias = "a"\n}\nprovider "aws" {\n  alias = "b"\n}\n'
+            'module "copy" {\n  source = "./child"\n  providers = {\n    aws.src = aws.a\n    aws.dst   = aws.b\n  }\n}\n')
+    assert summaries(module_dir, root, **{"child/main.tf": child}) == []
+    out, diags = format_source(root, "main.tf")
+    assert not diags and "    aws.src = aws.a\n    aws.dst = aws.b\n" in out
+
+
+def test_dotted_key_in_an_ordinary_object_is_ambiguous(module_dir):
+    text = 'locals {\n  a = { x.y = 1 }\n  b = { (local.k) = 1, "x.y" = 2 }\n  k = "k"\n}\n'
+    res, diags = diag_set(module_dir, {"main.tf": text})
+    assert diags == [("error", "Ambiguous attribute key")]
+    assert (res.diags[0].line, res.diags[0].col) == (2, 9)
