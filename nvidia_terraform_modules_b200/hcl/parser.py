@@ -889,7 +889,15 @@ def _strip_indent(parts: list) -> list:
 def parse(src: str, filename: str = "") -> tuple[A.Body, list[Diagnostic], list[Token]]:
     """Parse one file.  Returns (body, diagnostics, full token list)."""
     parser = Parser(src, filename)
-    body = parser.parse_file()
+    try:
+        body = parser.parse_file()
+    except RecursionError:
+        # hundreds of brackets inside one another: refuse the file rather than die in it
+        tok = parser.toks[min(parser.p, len(parser.toks) - 1)]
+        diag = Diagnostic(ERROR, "Expression nested too deeply",
+                          "This file nests brackets more deeply than this checker will follow.",
+                          filename, tok.line, tok.col, "syntax")
+        return A.Body(), parser.diags + [diag], parser.all
     return body, parser.diags, parser.all
 
 

@@ -225,3 +225,12 @@ def test_error_inside_nested_brackets_does_not_corrupt_newline_state():
     assert diags
     # parsing went on and later, well-formed items were still seen
     assert body.items[-1].name == "c"
+
+
+def test_absurd_nesting_is_a_diagnostic_not_a_crash():
+    from nvidia_terraform_modules_b200.fmt.command import format_source
+    src = "x = " + "[" * 3000 + "1" + "]" * 3000 + "\n"
+    out, diags = format_source(src, "deep.tf")
+    assert out == src and [d.summary for d in diags] == ["Expression nested too deeply"]
+    ok = "x = " + "[" * 60 + "1" + "]" * 60 + "\n"
+    assert format_source(ok, "ok.tf") == (ok, [])
