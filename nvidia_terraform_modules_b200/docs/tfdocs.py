@@ -84,9 +84,19 @@ def type_cell(m: Module, var: Variable) -> str:
 def default_cell(var: Variable) -> str:
     if not var.has_default:
         return "n/a"
-    if var.default is typeexpr.UNKNOWN:
-        return "n/a"
+    if var.default is typeexpr.UNKNOWN or _holds_unknown(var.default):
+        return "n/a"           # not a literal (itself an error: "Variables not allowed")
     return _code_cell(_json(var.default))
+
+
+def _holds_unknown(value) -> bool:
+    if value is typeexpr.UNKNOWN:
+        return True
+    if isinstance(value, dict):
+        return any(_holds_unknown(v) for v in value.values())
+    if isinstance(value, (list, tuple)):
+        return any(_holds_unknown(v) for v in value)
+    return False
 
 
 def leading_comment(m: Module, decl) -> Optional[str]:

@@ -185,3 +185,12 @@ def test_providers_table_is_checked_by_name(module_dir, tmp_path):
     # a version column of "n/a" (README generated before a lock file existed) is not drift
     readme.write_text(fresh.replace(rows[0], rows[0].rsplit("|", 2)[0] + "| n/a |"))
     assert check_readme(m, str(readme)) == []
+
+
+def test_a_default_that_is_not_a_literal_renders_as_n_a(module_dir):
+    """Found by the fuzzer: ``default = [var.a]`` (an error in its own right) made the
+    table generator raise inside json.dumps."""
+    d = module_dir({"main.tf": 'variable "a" {}\nvariable "v" {\n  default = ([var.a])\n}\n'})
+    m = load_module(d, d)
+    row = next(ln for ln in render(m).splitlines() if "input_v" in ln)
+    assert row.endswith("| `list` | n/a | no |")
