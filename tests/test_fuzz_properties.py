@@ -224,3 +224,66 @@ def test_validate_survives_noise(tmp_path_factory, src, release):
     (d / "main.tf").write_text(src, encoding="utf-8", newline="")
     clear_caches()
     validate_module(str(d), str(d), release)
+
+
+# ---------------------------------------------------- richer, Terraform-shaped expressions
+REFS = st.sampled_from([
+    "var.v", "var.w", "var.nope", "local.x", "local.y", "a_b.c", "a_b.c.id", "a_b.c[0].id", "a_b.d[\"k\"].id",
+    "a_b.c[*].id", "a_b.c.*.id", "data.a_b.c.id", "data.a_b.c[0]", "module.m", "module.m.out", "module.m[0].out",
+    "module.m[\"k\"]", "ephemeral.a_b.e.v", "count.index", "each.key", "each.value.x", "self.id", "path.module",
+    "path.nope", "terraform.workspace", "terraform.applying", "var", "local", "module", "data.a_b", "a_b", "each",
+    "x.value", "x.key", "null", "true", "12", "\"s\"", "\"a${var.v}b\"", "\"${local.x}\"", "<<EOT\nh ${var.v}\nEOT\n",
+])
+FUNCS = st.sampled_from(["upper", "length", "merge", "one", "try", "can", "lookup", "format", "list", "map", "nosuch",
+                         "startswith", "provider::p::f", "core::upper", "templatestring", "alltrue", "sensitive"])
+
+
+def rich_exprs():
+    def grow(inner):
+        return st.one_of(
+            st.tuples(FUNCS, st.lists(inner, max_size=3), st.booleans()).map(
+                lambda t: f"{t[0]}({', '.join(t[1])}{'...' if t[2] and t[1] else ''})"),
+            st.tuples(inner, inner, inner).map(lambda t: f"{t[0]} ? {t[1]} : {t[2]}"),
+            st.tuples(inner, st.sampled_from(["+", "-", "*", "/", "%", "==", "!=", "<", ">=", "&&", "||"]), inner).map(
+                lambda t: f"{t[0]} {t[1]} {t[2]}"),
+            inner.map(lambda e: f"({e})"), inner.map(lambda e: f"!{e}"), inner.map(lambda e: f"-{e}"),
+            st.lists(inner, max_size=3).map(lambda xs: "[" + ", ".join(xs) + "]"),
+            st.lists(st.tuples(st.sampled_from(["a", "b", "\"q\"", "(var.v)", "a.b", "true"]), inner), max_size=3).map(
+                lambda kvs: "{ " + ", ".join(f"{k} = {v}" for k, v in kvs) + " }" if kvs else "{}"),
+            st.tuples(inner, inner).map(lambda t: f"[for x in {t[0]} : {t[1]}]"),
+            st.tuples(inner, inner, inner).map(lambda t: f"{{ for k, x in {t[0]} : {t[1]} => {t[2]} }}"),
+            st.tuples(inner, inner).map(lambda t: f"{t[0]}[{t[1]}]"),
+            inner.map(lambda e: f"{e}.attr"), inner.map(lambda e: f"{e}[*].attr"),
+        )
+    return st.recursive(REFS, grow, max_leaves=6)
+
+
+def rich_bodies(depth=2):
+    attr = st.tuples(INNER_NAME, rich_exprs()).map(lambda t: f"  {t[0]} = {t[1]}\n")
+    items = [attr, attr, attr]
+    if depth:
+        items.append(st.tuples(INNER_BLOCK, rich_bodies(depth - 1)).map(lambda t: f"  {t[0]} {{\n{t[1]}  }}\n"))
+    return st.lists(st.one_of(*items), max_size=5).map("".join)
+
+
+RICH_MODULE = st.lists(st.tuples(TOP_LEVEL, rich_bodies()).map(lambda t: f"{t[0]}{{\n{t[1]}}}\n"), max_size=6).map("".join)
+
+
+@COMMON
+@given(RICH_MODULE, RELEASES)
+def test_validate_lint_docs_and_fmt_survive_terraform_shaped_modules(tmp_path_factory, src, release):
+    from nvidia_terraform_modules_b200.check import clear_caches
+    from nvidia_terraform_modules_b200.config.validate import validate_module
+    from nvidia_terraform_modules_b200.docs.tfdocs import render
+    from nvidia_terraform_modules_b200.lint.rules import run_rules
+    d = _one_dir(tmp_path_factory, "rich")
+    (d / "main.tf").write_text(src)
+    clear_caches()
+    res = validate_module(str(d), str(d), release)
+    for diag in res.diags:
+        assert diag.summary and diag.line >= 0
+    run_rules(res)
+    render(res.module)
+    out, diags = format_source(src, "main.tf")
+    if not has_errors(diags):
+        assert format_source(out, "main.tf")[0] == out or "${" in src      # (nested "${"${x}"}" unwraps twice)
