@@ -227,7 +227,23 @@ class _Loader:
             self.m.files.append(SourceFile(disp, src, body, tokens))
             if has_errors(diags):
                 self.m.broken_files.add(disp)
-        self.m.restated = self.forced or tfversion.from_required_version(self.sniff_required_versions())
+        sniffed = self.sniff_required_versions()
+        self.m.restated = self.forced or tfversion.from_required_version(sniffed)
+        if self.forced is not None and self.forced.requested is not None:
+            # the release named on the command line must be one the module accepts, exactly as
+            # a Terraform binary of that release would refuse the configuration
+            asked = self.forced.requested
+            for text, where in sniffed:
+                cons, _ = try_parse_constraints(text)
+                if cons is not None and not tfversion.series_admitted(asked, [cons]):
+                    file, _, line = where.rpartition(":")
+                    self.m.diags.append(Diagnostic(
+                        ERROR, "Unsupported Terraform Core version",
+                        f"This configuration does not support Terraform version {tfversion.text(asked)}. To proceed, "
+                        "either choose another supported Terraform version or update this version constraint. "
+                        "Version constraints are normally set for good reason, so updating the constraint may lead "
+                        f"to other errors or unexpected behavior.\n\n(required_version = \"{text}\")",
+                        file, int(line), 0, "terraform-version"))
         # experiments apply to the whole module, whichever file happens to be read first
         for f in self.m.files:
             if f.path not in self.m.broken_files:

@@ -119,6 +119,7 @@ class Restated:
     release: Release
     source: str                    # human-readable: where the choice came from
     note: str = ""                 # set when the choice had to be clamped
+    requested: Optional[Release] = None     # what --terraform-version named, before any clamp
 
     def has(self, feature: str) -> bool:
         return self.release >= SINCE[feature]
@@ -144,7 +145,15 @@ def _clamp(release: Release, source: str) -> Restated:
 
 
 def from_flag(value: str) -> Restated:
-    return _clamp(parse_release(value), "--terraform-version")
+    asked = parse_release(value)
+    r = _clamp(asked, "--terraform-version")
+    return Restated(r.release, r.source, r.note, asked)
+
+
+def series_admitted(release: Release, constraints: Iterable[Constraints]) -> bool:
+    """Does any patch release of ``release`` satisfy every constraint?"""
+    cons = list(constraints)
+    return any(all(c.allows(Version(release[0], release[1], patch)) for c in cons) for patch in range(0, 40))
 
 
 def from_required_version(entries: list[tuple[str, str]]) -> Restated:

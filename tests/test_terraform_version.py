@@ -57,6 +57,18 @@ def test_release_comes_from_flag_then_required_version_then_default(module_dir):
     assert r.release == tfversion.NEWEST and "sets no floor" in r.source
 
 
+def test_a_named_release_the_module_excludes_is_refused_like_terraform_would(module_dir):
+    text = 'terraform {\n  required_version = ">= 1.2.4, < 1.6"\n}\n'
+    for asked, ok in (("1.1", False), ("1.2", True), ("1.5.7", True), ("1.6", False), ("1.14", False)):
+        res = run(module_dir, text, asked)
+        assert (errors(res) == []) is ok, asked
+        if not ok:
+            assert errors(res) == [("Unsupported Terraform Core version", 2)]
+            want = ".".join(asked.split(".")[:2])
+            assert res.diags[0].detail.startswith(f"This configuration does not support Terraform version {want}.")
+    assert errors(run(module_dir, text)) == []          # its own floor is always acceptable
+
+
 def test_releases_outside_the_restated_range_are_clamped_and_say_so(module_dir):
     r = run(module_dir, 'terraform {\n  required_version = ">= 0.12"\n}\n').module.restated
     assert r.release == tfversion.OLDEST and "read as 0.13" in r.describe()
