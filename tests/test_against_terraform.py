@@ -315,6 +315,7 @@ VALIDATE_CASES: dict[str, dict[str, str]] = {
     "module_version_on_local_source": {"main.tf": 'module "c" {\n  source  = "./child"\n  version = "1.0.0"\n'
                                                   '  label   = "a"\n}\n', **CHILD},
     "required_version_syntax": {"main.tf": 'terraform {\n  required_version = "~~> 1"\n}\n'},
+    "required_version_excludes_this_binary": {"main.tf": 'terraform {\n  required_version = "< 0.12.0"\n}\n'},
     "terraform_unsupported_argument": {"main.tf": 'terraform {\n  colour = "red"\n}\n'},
     "inconsistent_conditional": {"main.tf": 'locals {\n  a = true ? "x" : [1]\n}\n'},
     "deprecated_interpolation_only": {"main.tf": 'variable "a" {\n  default = "x"\n}\noutput "o" {\n  value = "${var.a}"\n}\n'},
