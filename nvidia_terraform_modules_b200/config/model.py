@@ -133,6 +133,13 @@ class RequiredProvider(Decl):
     source: Optional[str] = None
     constraint_text: Optional[str] = None
     constraints: Optional[Constraints] = None
+    aliases: tuple = ()       # configuration_aliases = [aws.src, aws.dst] -> ("src", "dst")
+
+    @property
+    def display(self) -> str:
+        """``hashicorp/aws``: the address the way Terraform prints it in messages."""
+        host, _, rest = self.fqn.partition("/")
+        return rest if host == "registry.terraform.io" else self.fqn
 
     @property
     def fqn(self) -> str:
@@ -923,6 +930,11 @@ class _Loader:
                               f.path, item.expr, "structure")
                 if isinstance(val.get("version"), str):
                     req.constraint_text = val["version"]
+                wanted = item.expr.get("configuration_aliases") if isinstance(item.expr, A.ObjectCons) else None
+                if isinstance(wanted, A.TupleCons):
+                    req.aliases = tuple(t.steps[0].value for t in wanted.items
+                                        if isinstance(t, A.ScopeTraversal) and t.root == name
+                                        and len(t.steps) == 1 and t.steps[0].kind == "attr")
             else:
                 self.diag(ERROR, "Invalid required_providers object",
                           "required_providers entries must be strings or objects.", f.path, item.expr, "structure")

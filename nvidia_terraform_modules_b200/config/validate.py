@@ -224,6 +224,23 @@ class Validator:
                 self.diag(ERROR, "Unsupported argument",
                           f"An argument named \"{name}\" is not expected here.", base, attr, "module-arguments")
         if child is not None:
+            handed = set()
+            pattr = b.body.attributes.get("providers")
+            if pattr is not None and isinstance(pattr.expr, A.ObjectCons):
+                for key, _ in pattr.expr.items:
+                    w = key.wrapped
+                    handed.add(key.bare_name or (w.dotted() if isinstance(w, A.ScopeTraversal) else ""))
+            for req in child.required_providers.values():
+                for alias in req.aliases:
+                    local = f"{req.name}.{alias}"
+                    if local not in handed:
+                        self.diag(ERROR, "Missing required provider configuration",
+                                  f"The child module requires an additional configuration for provider {req.display}, "
+                                  f"with the local name \"{local}\".\n\nRefer to the module's documentation to "
+                                  "understand the intended purpose of this additional provider configuration, and then "
+                                  f"add an entry for {local} in the \"providers\" meta-argument in the module block to "
+                                  "choose which provider configuration the module should use for that purpose.",
+                                  base, b, "module-arguments")
             for vname, var in child.variables.items():
                 if var.required and vname not in passed:
                     self.diag(ERROR, "Missing required argument",

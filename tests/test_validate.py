@@ -408,3 +408,15 @@ def test_dotted_key_in_an_ordinary_object_is_ambiguous(module_dir):
     res, diags = diag_set(module_dir, {"main.tf": text})
     assert diags == [("error", "Ambiguous attribute key")]
     assert (res.diags[0].line, res.diags[0].col) == (2, 9)
+
+
+def test_child_configuration_aliases_must_be_handed_over(module_dir):
+    child = ('terraform {\n  required_providers {\n    aws = {\n      source                = "hashicorp/aws"\n'
+             '      configuration_aliases = [aws.src, aws.dst]\n    }\n  }\n}\n')
+    root = ('provider "aws" {\n  alias = "a"\n}\nmodule "copy" {\n  source = "./child"\n  providers = {\n'
+            '    aws.src = aws.a\n  }\n}\nmodule "none" {\n  source = "./child"\n}\n')
+    res, diags = diag_set(module_dir, {"main.tf": root, "child/main.tf": child})
+    assert diags == [("error", "Missing required provider configuration")] * 3
+    assert [d.line for d in res.diags] == [4, 10, 10]
+    assert res.diags[0].detail.startswith('The child module requires an additional configuration for provider '
+                                          'hashicorp/aws, with the local name "aws.dst".')
