@@ -363,6 +363,44 @@ VALIDATE_CASES: dict[str, dict[str, str]] = {
                                                  '    command = "echo ${var.h}"\n  }\n}\n'},
     "depends_on_quoted": {"main.tf": 'resource "terraform_data" "a" {}\nresource "terraform_data" "b" {\n'
                                      '  depends_on = ["terraform_data.a"]\n}\n'},
+    "nullable_false_null_default": {"main.tf": 'variable "a" {\n  type     = string\n  nullable = false\n  default  = null\n}\n'},
+    "sensitive_not_bool": {"main.tf": 'variable "a" {\n  sensitive = "maybe"\n}\n'},
+    "locals_nested_block": {"main.tf": 'locals {\n  a = 1\n  nested {\n  }\n}\n'},
+    "count_negative": {"main.tf": 'resource "terraform_data" "a" {\n  count = -1\n}\n'},
+    "count_null": {"main.tf": 'resource "terraform_data" "a" {\n  count = null\n}\n'},
+    "count_string": {"main.tf": 'resource "terraform_data" "a" {\n  count = "many"\n}\n'},
+    "for_each_string": {"main.tf": 'resource "terraform_data" "a" {\n  for_each = "x"\n}\n'},
+    "count_wrong_attr": {"main.tf": 'resource "terraform_data" "a" {\n  count = 1\n  input = count.number\n}\n'},
+    "each_wrong_attr": {"main.tf": 'resource "terraform_data" "a" {\n  for_each = toset(["x"])\n  input    = each.index\n}\n'},
+    "depends_on_not_a_list": {"main.tf": 'resource "terraform_data" "a" {}\nresource "terraform_data" "b" {\n'
+                                         '  depends_on = terraform_data.a\n}\n'},
+    "module_lifecycle_block": {"main.tf": 'module "c" {\n  source = "./child"\n  label  = "a"\n  lifecycle {\n  }\n}\n',
+                               **CHILD},
+    "moved_missing_to": {"main.tf": 'moved {\n  from = terraform_data.a\n}\n'},
+    "import_missing_id": {"main.tf": 'import {\n  to = terraform_data.a\n}\nresource "terraform_data" "a" {}\n'},
+    "check_bad_name": {"main.tf": 'check "1x" {\n  assert {\n    condition     = true\n    error_message = "m"\n  }\n}\n'},
+    "duplicate_required_providers_entry": {"main.tf": 'terraform {\n  required_providers {\n    null = {\n'
+                                                      '      source = "hashicorp/null"\n    }\n  }\n'
+                                                      '  required_providers {\n    null = {\n'
+                                                      '      source = "hashicorp/null"\n    }\n  }\n}\n'},
+    "required_providers_bad_key": {"main.tf": 'terraform {\n  required_providers {\n    null = {\n'
+                                              '      source = "hashicorp/null"\n      colour = "red"\n    }\n  }\n}\n'},
+    "output_sensitive_not_bool": {"main.tf": 'output "o" {\n  value     = 1\n  sensitive = "yes"\n}\n'},
+    "attribute_redefined": {"main.tf": 'output "o" {\n  value = 1\n  value = 2\n}\n'},
+    "legacy_index_warning_free": {"main.tf": 'locals {\n  l = [1, 2]\n  a = local.l.0\n}\n'},
+    "for_expression_scopes": {"main.tf": 'locals {\n  l = ["a"]\n  a = [for i, v in local.l : "${i}${v}" if v != ""]\n'
+                                         '  b = { for v in local.l : v => i }\n}\n'},
+    "template_directive_scopes": {"main.tf": 'locals {\n  l = ["a"]\n  a = "%{for v in local.l}${v}%{endfor}${v}"\n}\n'},
+    "provisioner_on_failure_bad": {"main.tf": 'resource "terraform_data" "a" {\n  provisioner "local-exec" {\n'
+                                              '    on_failure = retry\n    command    = "x"\n  }\n}\n'},
+    "provisioner_quoted_keyword": {"main.tf": 'resource "terraform_data" "a" {\n  provisioner "local-exec" {\n'
+                                              '    when    = "destroy"\n    command = "x"\n  }\n}\n'},
+    "self_in_precondition": {"main.tf": 'resource "terraform_data" "a" {\n  lifecycle {\n    precondition {\n'
+                                        '      condition     = self.id != ""\n      error_message = "m"\n    }\n  }\n}\n'},
+    "quoted_type_keyword": {"main.tf": 'variable "a" {\n  type = "string"\n}\n'},
+    "legacy_type_hint": {"main.tf": 'variable "a" {\n  type = "list(string)"\n}\n'},
+    "optional_outside_object": {"main.tf": 'variable "a" {\n  type = optional(string)\n}\n'},
+    "type_constructor_arity": {"main.tf": 'variable "a" {\n  type = list(string, number)\n}\n'},
     "scoped_data_source": {"main.tf": 'check "c" {\n  data "terraform_remote_state" "s" {\n    backend = "local"\n  }\n'
                                       '  assert {\n    condition     = data.terraform_remote_state.s.outputs != null\n'
                                       '    error_message = "State."\n  }\n}\n'
@@ -378,6 +416,19 @@ UNCERTAIN = {
     "resource_ignore_changes_keyword": "wording of a non-list, non-keyword ignore_changes",
     "removed_function_list": "summary of the error a removed function raises",
     "scoped_data_source": "whether validate or only plan reports a reference to a scoped data source",
+    "count_null": "wording for a null count",
+    "count_string": "wording for a count that is not a number",
+    "for_each_string": "wording for a for_each that is a string literal",
+    "count_negative": "whether validate or only plan rejects a negative literal count",
+    "sensitive_not_bool": "wording for a non-boolean sensitive argument",
+    "output_sensitive_not_bool": "wording for a non-boolean sensitive argument",
+    "legacy_index_warning_free": "whether `.0` still parses silently",
+    "template_directive_scopes": "placement of the error for a name used after its %{for} has ended",
+    "module_lifecycle_block": "wording for a reserved block type inside a module call",
+    "check_bad_name": "wording for an invalid check block name",
+    "optional_outside_object": "wording for optional() outside an object type",
+    "type_constructor_arity": "wording for a type constructor with too many arguments",
+    "duplicate_required_providers_entry": "two required_providers blocks in one terraform block",
 }
 
 # with $TF_PLUGIN_MIRROR: providers the reference's example lock files pin
