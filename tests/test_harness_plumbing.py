@@ -32,7 +32,7 @@ def test_harness_runs_end_to_end_against_the_shim():
     tail = p.stdout[-3000:] + p.stderr[-2000:]
     assert p.returncode == 0, tail
     m = re.search(r"(\d+) passed", p.stdout)
-    assert m and int(m.group(1)) >= 76, tail          # fmt corpus + command + questions + validate cases + docs
+    assert m and int(m.group(1)) >= 95, tail          # fmt corpus + command + questions + validate cases + docs
     assert "failed" not in p.stdout.splitlines()[-1], tail
     assert "$TF_PLUGIN_MIRROR not set" in p.stdout      # provider-backed cases say why they did not run
 
